@@ -1,0 +1,401 @@
+"""diff_gaussian_sampling_b200 — B200-native drop-in for `diff_gaussian_sampling`.
+
+Mirrors the reference's Python surface (diff_gaussian_sampling/__init__.py:21-36,52-77,
+128-317): the same module-level functions, the same torch.autograd.Function classes with
+the same 10-argument forward / 11-tuple backward contract, the same GaussianSampler holder
+and the same debug snapshot behaviour (:38-50).  The pybind module `_C` (ext.cpp:19-32) is
+replaced by `_C` below: twelve functions with the reference's names and positional
+arguments, implemented over the C ABI of libdgs_b200.so (include/dgs_b200.h) through
+ctypes.  torch is used for device memory and the current stream only.
+
+Extensions that do not change the reference signatures:
+  * `preprocess_gaussians(..., bounds=(lo, hi))` / `GaussianSampler.preprocess(..., bounds=)`
+    bins with given global sample bounds (multi-GPU point sharding);
+  * D == 3 is supported (the reference silently returns zeros there).
+"""
+from __future__ import annotations
+
+import ctypes
+from collections import OrderedDict
+
+import torch
+
+from . import _lib
+from ._lib import Plan
+
+__all__ = [
+    "GaussianSampler", "preprocess_gaussians", "preprocess_aggregate", "sample_gaussians",
+    "sample_gaussians_derivative", "sample_gaussians_laplacian", "sample_gaussians_third_derivative",
+    "aggregate_neighbors", "plan_of", "count_pairs",
+]
+
+# ---------------------------------------------------------------------------------------
+# plan bookkeeping: the reference passes only tensors + num_rendered between preprocess and
+# forward/backward, so the host-side plan is remembered per binning buffer (and can always be
+# recovered from the buffer itself with one small D2H copy).
+# ---------------------------------------------------------------------------------------
+_PLANS: "OrderedDict[tuple, Plan]" = OrderedDict()
+_PLANS_MAX = 64
+
+
+def _remember(buf: torch.Tensor, plan: Plan):
+    key = (buf.device.index, buf.data_ptr(), buf.numel())
+    _PLANS[key] = plan
+    _PLANS.move_to_end(key)
+    while len(_PLANS) > _PLANS_MAX:
+        _PLANS.popitem(last=False)
+
+
+def plan_of(binning_buffer: torch.Tensor, num_rendered: int) -> Plan:
+    key = (binning_buffer.device.index, binning_buffer.data_ptr(), binning_buffer.numel())
+    plan = _PLANS.get(key)
+    if plan is not None and plan.num_rendered == int(num_rendered):
+        return plan
+    lib = _lib.load()
+    plan = Plan()
+    with torch.cuda.device(binning_buffer.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.dgs_plan_from_buffer(binning_buffer.data_ptr(), binning_buffer.numel(), int(num_rendered),
+                                            ctypes.byref(plan), st), "dgs_plan_from_buffer")
+    _remember(binning_buffer, plan)
+    return plan
+
+
+def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: this library has no CPU path")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32 (got {t.dtype})")
+    return t.contiguous()
+
+
+_FN_ORDER = {"gaussian": 0, "derivative": 1, "laplacian": 2, "third": 3}
+
+
+class _NativeOps:
+    """The twelve entry points of the reference's pybind module (ext.cpp:20-31), same names and
+    positional arguments, over the C ABI."""
+
+    # -- preprocess_gaussians (sample_points.cu:37-98) ----------------------------------
+    @staticmethod
+    def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None):
+        lib = _lib.load()
+        means = _f32c(means, "means"); covariances = _f32c(covariances, "covariances")
+        conics = _f32c(conics, "conics"); samples = _f32c(samples, "samples")
+        P, D = means.shape[0], means.shape[-1]
+        N = samples.shape[0]
+        dev = means.device
+        u8 = dict(dtype=torch.uint8, device=dev)
+        radii = torch.zeros(P, dtype=torch.float32, device=dev)
+        if P == 0 or N == 0:                                   # sample_points.cu:69 early-out
+            e = torch.empty(0, **u8)
+            return 0, e, e.clone(), e.clone(), e.clone(), radii
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream().cuda_stream
+            plan = Plan()
+            geom = torch.empty(lib.dgs_geom_bytes(P, N, D), **u8)
+            bptr = None
+            if bounds is not None:
+                lo, hi = bounds
+                arr = (ctypes.c_float * (2 * D))(*[float(x) for x in list(lo)[:D] + list(hi)[:D]])
+                bptr = ctypes.cast(arr, ctypes.c_void_p)
+            _lib.check(lib.dgs_plan_begin(means.data_ptr(), conics.data_ptr(), samples.data_ptr(), P, N, D, bptr,
+                                          float(tau) if tau else 0.0, geom.data_ptr(), geom.numel(),
+                                          ctypes.byref(plan), st), "dgs_plan_begin")
+            sbuf = torch.empty(plan.sample_binning_bytes, **u8)
+            sample_ranges = torch.zeros(plan.ranges_bytes, **u8)          # sample_points.cu:77
+            _lib.check(lib.dgs_preprocess_count(ctypes.byref(plan), means.data_ptr(), covariances.data_ptr(),
+                                                samples.data_ptr(), radii.data_ptr(), geom.data_ptr(), geom.numel(),
+                                                sbuf.data_ptr(), sbuf.numel(), sample_ranges.data_ptr(), st),
+                       "dgs_preprocess_count")
+            gbuf = torch.empty(plan.binning_bytes, **u8)
+            ranges = torch.zeros(plan.ranges_bytes, **u8)                 # sample_points.cu:76
+            _lib.check(lib.dgs_preprocess_bin(ctypes.byref(plan), means.data_ptr(), radii.data_ptr(), geom.data_ptr(),
+                                              geom.numel(), gbuf.data_ptr(), gbuf.numel(), sbuf.data_ptr(), sbuf.numel(),
+                                              ranges.data_ptr(), st), "dgs_preprocess_bin")
+            if debug:
+                torch.cuda.synchronize(dev)                    # CHECK_CUDA semantics (auxiliary.h:33-40)
+        _remember(gbuf, plan)
+        return int(plan.num_rendered), gbuf, sbuf, ranges, sample_ranges, radii
+
+    # -- forward (sample_points.cu:100-143,198-297) -------------------------------------
+    @staticmethod
+    def _forward(fn, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
+                 sample_ranges, debug):
+        lib = _lib.load()
+        means = _f32c(means, "means"); values = _f32c(values, "values")
+        conics = _f32c(conics, "conics"); samples = _f32c(samples, "samples")
+        P, D = means.shape[0], means.shape[-1]
+        N, C = samples.shape[0], values.shape[-1]
+        shape = (N,) + (D,) * fn + (C,)
+        if P == 0 or N == 0 or binning_buffer.numel() == 0:     # sample_points.cu:119
+            return torch.zeros(shape, dtype=torch.float32, device=means.device)
+        plan = plan_of(binning_buffer, num_rendered)
+        if plan.P != P or plan.N != N or plan.D != D:
+            raise RuntimeError("binning buffers were built for different tensor shapes")
+        out = torch.empty(shape, dtype=torch.float32, device=means.device)
+        with torch.cuda.device(means.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_sample_forward(ctypes.byref(plan), fn, C, means.data_ptr(), values.data_ptr(),
+                                              conics.data_ptr(), samples.data_ptr(), binning_buffer.data_ptr(),
+                                              sample_binning_buffer.data_ptr(), ranges.data_ptr(),
+                                              sample_ranges.data_ptr(), out.data_ptr(), st), "dgs_sample_forward")
+            if debug:
+                torch.cuda.synchronize(means.device)
+        return out
+
+    # -- backward (sample_points.cu:145-196,299-372) ------------------------------------
+    @staticmethod
+    def _backward(fn, means, values, conics, samples, num_rendered, dL_dout, binning_buffer, sample_binning_buffer,
+                  ranges, sample_ranges, debug):
+        lib = _lib.load()
+        means = _f32c(means, "means"); values = _f32c(values, "values")
+        conics = _f32c(conics, "conics"); samples = _f32c(samples, "samples")
+        dL_dout = _f32c(dL_dout, "dL_dout")
+        P, D = means.shape[0], means.shape[-1]
+        N, C = samples.shape[0], values.shape[-1]
+        T = D * (D + 1) // 2
+        # one allocation, three views: a multi-GPU caller can allreduce `flat` in one call
+        flat = torch.zeros(P * (D + C + T), dtype=torch.float32, device=means.device)   # sample_points.cu:165-167
+        dmeans = flat[:P * D].view(P, D)
+        dvalues = flat[P * D:P * (D + C)].view(P, C)
+        dconics = flat[P * (D + C):].view(P, T)
+        if P == 0 or N == 0 or binning_buffer.numel() == 0:     # sample_points.cu:169
+            return dmeans, dvalues, dconics
+        plan = plan_of(binning_buffer, num_rendered)
+        with torch.cuda.device(means.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_sample_backward(ctypes.byref(plan), fn, C, means.data_ptr(), values.data_ptr(),
+                                               conics.data_ptr(), samples.data_ptr(), dL_dout.data_ptr(),
+                                               binning_buffer.data_ptr(), sample_binning_buffer.data_ptr(),
+                                               ranges.data_ptr(), sample_ranges.data_ptr(), dmeans.data_ptr(),
+                                               dvalues.data_ptr(), dconics.data_ptr(), st), "dgs_sample_backward")
+            if debug:
+                torch.cuda.synchronize(means.device)
+        return dmeans, dvalues, dconics
+
+    @staticmethod
+    def sample_gaussians(*a): return _NativeOps._forward(0, *a)
+    @staticmethod
+    def sample_gaussians_derivative(*a): return _NativeOps._forward(1, *a)
+    @staticmethod
+    def sample_gaussians_laplacian(*a): return _NativeOps._forward(2, *a)
+    @staticmethod
+    def sample_gaussians_third_derivative(*a): return _NativeOps._forward(3, *a)
+    @staticmethod
+    def sample_gaussians_backward(*a): return _NativeOps._backward(0, *a)
+    @staticmethod
+    def sample_gaussians_derivative_backward(*a): return _NativeOps._backward(1, *a)
+    @staticmethod
+    def sample_gaussians_laplacian_backward(*a): return _NativeOps._backward(2, *a)
+    @staticmethod
+    def sample_gaussians_third_derivative_backward(*a): return _NativeOps._backward(3, *a)
+
+    # -- aggregate_neighbors (aggregate_neighbors.cu:323-475): SURVEY.md §8 rows a-16..a-19 --
+    @staticmethod
+    def preprocess_aggregate(*a):
+        raise NotImplementedError("aggregate_neighbors is not built yet in libdgs_b200 (SURVEY.md §8 a-16..a-19)")
+    aggregate_neighbors = preprocess_aggregate
+    aggregate_neighbors_backward = preprocess_aggregate
+
+
+_C = _NativeOps
+
+
+# ---------------------------------------------------------------------------------------
+# module-level API, same names / argument order as diff_gaussian_sampling/__init__.py:21-77
+# ---------------------------------------------------------------------------------------
+def cpu_deep_copy_tuple(input_tuple):
+    return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
+
+
+def call_debug(func, debug, name, *args, **kwargs):
+    """debug=True: keep a CPU copy of the arguments and dump it to snapshot_<name>.dump when the
+    native call raises (reference __init__.py:38-50)."""
+    if debug:
+        cpu_args = cpu_deep_copy_tuple(args)
+        try:
+            return func(*args, **kwargs)
+        except Exception:
+            torch.save(cpu_args, "snapshot_{}.dump".format(name))
+            print("\nAn error occured in {}. Please forward snapshot_{}.dump for debugging.".format(name, name))
+            raise
+    return func(*args, **kwargs)
+
+
+def sample_gaussians(debug, *args):
+    return _SampleGaussians.apply(debug, *args)
+
+
+def sample_gaussians_derivative(debug, *args):
+    return _SampleGaussiansDerivative.apply(debug, *args)
+
+
+def sample_gaussians_laplacian(debug, *args):
+    return _SampleGaussiansLaplacian.apply(debug, *args)
+
+
+def sample_gaussians_third_derivative(debug, *args):
+    return _SampleGaussiansThirdDerivative.apply(debug, *args)
+
+
+def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None):
+    args = (means, values, covariances, conics, samples, debug)
+    return call_debug(_C.preprocess_gaussians, debug, "preprocess", *args, bounds=bounds, tau=tau)
+
+
+def preprocess_aggregate(means, conics, radii, debug):
+    return call_debug(_C.preprocess_aggregate, debug, "preprocess_agg", means, conics, radii, debug)
+
+
+def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform,
+                        indices, ranges, dists, densities, inv_total_densities, debug):
+    return _AggregateNeighbors.apply(features, transform, queries, keys, frequencies, distance_transform,
+                                     indices, ranges, dists, densities, inv_total_densities, debug)
+
+
+def call_forward(ctx, func, name, *args):
+    means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, debug = args
+    out_values = call_debug(func, debug, name, *args)
+    ctx.debug = debug
+    ctx.num_rendered = num_rendered
+    ctx.save_for_backward(means, values, conics, samples, binning_buffer, sample_binning_buffer, ranges, sample_ranges)
+    return out_values
+
+
+def call_backward(ctx, func, grad_out, name):
+    num_rendered = ctx.num_rendered
+    debug = ctx.debug
+    means, values, conics, samples, binning_buffer, sample_binning_buffer, ranges, sample_ranges = ctx.saved_tensors
+    args = (means, values, conics, samples, num_rendered, grad_out, binning_buffer, sample_binning_buffer, ranges,
+            sample_ranges, debug)
+    grad_means, grad_values, grad_conics = call_debug(func, debug, name, *args)
+    # grads for the 10 forward inputs (the reference returns 11 entries, one trailing None too many)
+    return (grad_means, grad_values, grad_conics, None, None, None, None, None, None, None)
+
+
+class _SampleGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *args):
+        return call_forward(ctx, _C.sample_gaussians, "fw", *args)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        return call_backward(ctx, _C.sample_gaussians_backward, grad_out, "bw")
+
+
+class _SampleGaussiansDerivative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *args):
+        return call_forward(ctx, _C.sample_gaussians_derivative, "der_fw", *args)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        return call_backward(ctx, _C.sample_gaussians_derivative_backward, grad_out, "der_bw")
+
+
+class _SampleGaussiansLaplacian(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *args):
+        return call_forward(ctx, _C.sample_gaussians_laplacian, "lap_fw", *args)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        return call_backward(ctx, _C.sample_gaussians_laplacian_backward, grad_out, "lap_bw")
+
+
+class _SampleGaussiansThirdDerivative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *args):
+        return call_forward(ctx, _C.sample_gaussians_third_derivative, "3_fw", *args)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        return call_backward(ctx, _C.sample_gaussians_third_derivative_backward, grad_out, "3_bw")
+
+
+class _AggregateNeighbors(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, features, transform, queries, keys, frequencies, distance_transform,
+                indices, ranges, dists, densities, inv_total_densities, debug):
+        args = (features, transform, queries, keys, frequencies, distance_transform,
+                indices, ranges, dists, densities, inv_total_densities, debug)
+        weights, embeddings, factors, neighbor_features = call_debug(_C.aggregate_neighbors, debug, "aggregate", *args)
+        ctx.debug = debug
+        ctx.save_for_backward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges,
+                              dists, densities, inv_total_densities, weights, embeddings, factors)
+        return neighbor_features
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
+         inv_total_densities, weights, embeddings, factors) = ctx.saved_tensors
+        grads = call_debug(_C.aggregate_neighbors_backward, ctx.debug, "aggregate_bw",
+                           features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                           densities, weights, embeddings, factors, inv_total_densities, grad_out, ctx.debug)
+        return tuple(grads) + (None,) * 6
+
+
+class GaussianSampler:
+    """Stateful holder, same methods as the reference's (diff_gaussian_sampling/__init__.py:214-317)."""
+
+    def __init__(self, debug=False):
+        self.debug = debug
+
+    def preprocess(self, means, values, covariances, conics, samples, bounds=None):
+        num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii = \
+            preprocess_gaussians(means, values, covariances, conics, samples, self.debug, bounds=bounds)
+        self.means = means
+        self.values = values
+        self.conics = conics
+        self.samples = samples
+        self.num_rendered = num_rendered
+        self.binning_buffer = binning_buffer
+        self.sample_binning_buffer = sample_binning_buffer
+        self.ranges = ranges
+        self.sample_ranges = sample_ranges
+        self.radii = radii
+
+    def _args(self):
+        return (self.means, self.values, self.conics, self.samples, self.num_rendered, self.binning_buffer,
+                self.sample_binning_buffer, self.ranges, self.sample_ranges, self.debug)
+
+    def sample_gaussians(self):
+        return sample_gaussians(*self._args())
+
+    def sample_gaussians_derivative(self):
+        return sample_gaussians_derivative(*self._args())
+
+    def sample_gaussians_laplacian(self):
+        return sample_gaussians_laplacian(*self._args())
+
+    def sample_gaussians_third_derivative(self):
+        return sample_gaussians_third_derivative(*self._args())
+
+    def preprocess_aggregate(self):
+        # the reference overwrites self.ranges here (its __init__.py:298), which breaks a later
+        # sample_gaussians(); the neighbour CSR is kept under its own name instead.
+        indices, nbr_ranges, dists, densities, inv_total_densities = \
+            preprocess_aggregate(self.means, self.conics, self.radii, self.debug)
+        self.indices = indices
+        self.neighbor_ranges = nbr_ranges
+        self.dists = dists
+        self.densities = densities
+        self.inv_total_densities = inv_total_densities
+
+    def aggregate_neighbors(self, features, transform, queries, keys, frequencies, distance_transform):
+        return aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform,
+                                   self.indices, self.neighbor_ranges, self.dists, self.densities,
+                                   self.inv_total_densities, self.debug)
+
+
+def count_pairs(binning_buffer, sample_binning_buffer, num_rendered, fn=0) -> int:
+    """(Gaussian, sample) pairs the accumulation kernels evaluate for function `fn` (roofline accounting)."""
+    lib = _lib.load()
+    plan = plan_of(binning_buffer, num_rendered)
+    counter = torch.zeros(1, dtype=torch.int64, device=binning_buffer.device)
+    with torch.cuda.device(binning_buffer.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.dgs_count_pairs(ctypes.byref(plan), fn, binning_buffer.data_ptr(), sample_binning_buffer.data_ptr(),
+                                       counter.data_ptr(), st), "dgs_count_pairs")
+    return int(counter.item())

@@ -1,0 +1,434 @@
+// dgs_api.cu — the C ABI of libdgs_b200.so (include/dgs_b200.h): plan, buffer layout and
+// stream-ordered orchestration of the kernels.  Replaces the reference's host glue
+// (sample_points.cu:37-372) and sampler runtime (cuda_sampler/sampler_impl.cu:191-405).
+// Nothing here allocates device memory or touches torch.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+#include "dgs_common.cuh"
+#include "dgs_preprocess.cuh"
+
+static thread_local char g_err[512] = "";
+void dgs_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" __attribute__((visibility("default"))) const char* dgs_last_error(void) { return g_err; }
+extern "C" __attribute__((visibility("default"))) int dgs_abi_version(void) { return DGS_ABI_VERSION; }
+
+// ---------------------------------------------------------------------------------------
+// layouts
+// ---------------------------------------------------------------------------------------
+extern "C" __attribute__((visibility("default"))) size_t dgs_public_bytes(uint64_t L) {
+    size_t o = 0;
+    o = dgs_a128(o + 4 * L);   // point_list
+    o = dgs_a128(o + 4 * L);   // point_list_unsorted
+    o = dgs_a128(o + 8 * L);   // point_list_keys
+    o = dgs_a128(o + 8 * L);   // point_list_keys_unsorted
+    return o;
+}
+struct PublicArrays {
+    uint32_t* list; uint32_t* list_unsorted; uint64_t* keys; uint64_t* keys_unsorted;
+};
+static PublicArrays public_arrays(void* buf, uint64_t L) {
+    uint8_t* b = (uint8_t*)buf;
+    PublicArrays p;
+    size_t o = 0;
+    p.list = (uint32_t*)(b + o); o = dgs_a128(o + 4 * L);
+    p.list_unsorted = (uint32_t*)(b + o); o = dgs_a128(o + 4 * L);
+    p.keys = (uint64_t*)(b + o); o = dgs_a128(o + 8 * L);
+    p.keys_unsorted = (uint64_t*)(b + o);
+    return p;
+}
+
+struct GeomLayout {
+    size_t hdr, crec, touched, offsets, n1, n1_off, scan_tmp, total;
+};
+static GeomLayout geom_layout(int64_t P) {
+    GeomLayout g;
+    const size_t p = (size_t)(P > 0 ? P : 1);
+    size_t o = 0;
+    g.hdr = o; o = dgs_a128(o + sizeof(DgsDevHeader));
+    g.crec = o; o = dgs_a128(o + p * sizeof(DgsCullRec));
+    g.touched = o; o = dgs_a128(o + p * 4);
+    g.offsets = o; o = dgs_a128(o + p * 4);
+    g.n1 = o; o = dgs_a128(o + p * 4);
+    g.n1_off = o; o = dgs_a128(o + p * 4);
+    g.scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes(p));
+    g.total = o;
+    return g;
+}
+extern "C" __attribute__((visibility("default"))) size_t dgs_geom_bytes(int64_t P, int64_t N, int D) {
+    (void)N; (void)D;
+    return geom_layout(P).total;
+}
+
+// uint32 getHigherMsb(uint32 n)   (sampler_impl.cu:39-50)
+static uint32_t higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+static int ceil_log2(uint64_t n) {
+    int b = 0;
+    while (((uint64_t)1 << b) < n) b++;
+    return b;
+}
+
+// sample-side temporary region (inside the sample binning buffer, after the persistent arrays)
+struct SampleTmp {
+    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, total;
+};
+static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
+    SampleTmp t;
+    const size_t n = (size_t)(pl->N > 0 ? pl->N : 1);
+    size_t o = 0;
+    t.tile_of = o; o = dgs_a128(o + n * 4);
+    t.rank_of = o; o = dgs_a128(o + n * 4);
+    t.sort_tmp = o; o = dgs_a128(o + dgs_sort_tmp_bytes(n));
+    t.scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes((int64_t)pl->n_fine + 1));
+    t.alt_keys = o; if (pl->sort_bits > 8) o = dgs_a128(o + n * 8);
+    t.alt_vals = o; if (pl->sort_bits > 8) o = dgs_a128(o + n * 4);
+    t.total = o;
+    return t;
+}
+
+static void sample_layout(dgs_plan_t* pl) {
+    const size_t n = (size_t)(pl->N > 0 ? pl->N : 1);
+    size_t o = dgs_public_bytes((uint64_t)pl->N);
+    pl->s_plan_off = o; o = dgs_a128(o + sizeof(dgs_plan_t));
+    pl->s_fine_start_off = o; o = dgs_a128(o + ((size_t)pl->n_fine + 1) * 4);
+    pl->s_fine_ids_off = o; o = dgs_a128(o + n * 4);
+    pl->s_fine_xyz_off = o; o = dgs_a128(o + n * 4 * pl->D);
+    pl->s_fine_aabb_off = o; o = dgs_a128(o + (size_t)pl->n_fine * 32);
+    pl->s_coarse_aabb_off = o; o = dgs_a128(o + (size_t)pl->n_coarse * 32);
+    pl->s_tmp_off = o; o += sample_tmp_layout(pl).total;
+    pl->sample_binning_bytes = o + 128;
+}
+
+// Gaussian-side temporary region (inside the binning buffer)
+struct GaussTmp {
+    size_t l1_keys_u, l1_vals_u, l1_keys_s, l1_alt_k, l1_alt_v, l1_sort_tmp, pub_sort_tmp, pub_alt_k, pub_alt_v, total;
+};
+static GaussTmp gauss_tmp_layout(const dgs_plan_t* pl) {
+    GaussTmp t;
+    const size_t e = (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1);
+    const size_t L = (size_t)(pl->num_rendered > 0 ? pl->num_rendered : 1);
+    const bool l1_multi = ceil_log2((uint64_t)pl->n_coarse) > 8;
+    size_t o = 0;
+    t.l1_keys_u = o; o = dgs_a128(o + e * 4);
+    t.l1_vals_u = o; o = dgs_a128(o + e * 4);
+    t.l1_keys_s = o; o = dgs_a128(o + e * 4);
+    t.l1_alt_k = o; if (l1_multi) o = dgs_a128(o + e * 4);
+    t.l1_alt_v = o; if (l1_multi) o = dgs_a128(o + e * 4);
+    t.l1_sort_tmp = o; o = dgs_a128(o + dgs_sort_tmp_bytes(e));
+    t.pub_sort_tmp = o; o = dgs_a128(o + dgs_sort_tmp_bytes(L));
+    t.pub_alt_k = o; if (pl->sort_bits > 8) o = dgs_a128(o + L * 8);
+    t.pub_alt_v = o; if (pl->sort_bits > 8) o = dgs_a128(o + L * 4);
+    t.total = o;
+    return t;
+}
+
+static void gauss_layout(dgs_plan_t* pl) {
+    const size_t p = (size_t)(pl->P > 0 ? pl->P : 1);
+    size_t o = dgs_public_bytes((uint64_t)pl->num_rendered);
+    pl->g_plan_off = o; o = dgs_a128(o + sizeof(dgs_plan_t));
+    pl->g_crec_off = o; o = dgs_a128(o + p * sizeof(DgsCullRec));
+    pl->g_l1_start_off = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
+    pl->g_l1_ids_off = o; o = dgs_a128(o + (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * 4);
+    pl->g_sort_tmp_off = o; o += gauss_tmp_layout(pl).total;
+    pl->binning_bytes = o + 128;
+}
+
+// ---------------------------------------------------------------------------------------
+// step 1: bounds, grid, cull records, tile hierarchy
+// ---------------------------------------------------------------------------------------
+static int choose_tiles(dgs_plan_t* pl) {
+    const int D = pl->D;
+    const double per_cell = (double)pl->N / (double)(pl->blocks > 0 ? pl->blocks : 1);
+    const double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 176.0);
+    double f = pow(per_cell / target, 1.0 / D);
+    int F = (int)floor(f);
+    if (F < 1) F = 1;
+    const int fpc_default = D == 1 ? 8 : (D == 2 ? 4 : 2);
+    int T1 = (F + fpc_default - 1) / fpc_default;
+    // keep a Gaussian's tau-box from covering too many coarse tiles (list entries ~ P * prod(2R/w + 1))
+    if (pl->mean_extent > 0.f) {
+        const double k = D == 1 ? 0.765 : (D == 2 ? 0.467 : 0.33);
+        int cap = (int)floor(k / (double)pl->mean_extent);
+        if (cap < 1) cap = 1;
+        if (T1 > cap) T1 = cap;
+    }
+    if (T1 < 1) T1 = 1;
+    int fpc = (F + T1 - 1) / T1;
+    const int fpc_max = D == 1 ? 64 : (D == 2 ? 8 : 4);
+    if (fpc > fpc_max) fpc = fpc_max;
+    // bound the number of tiles
+    auto ipow = [](int64_t b, int e) { int64_t r = 1; for (int i = 0; i < e; i++) r *= b; return r; };
+    const int64_t max_coarse = 1 << 22, max_fine = 1 << 24;
+    while (T1 > 1 && (int64_t)pl->n_cells_ext * ipow(T1, D) > max_coarse) T1--;
+    while (fpc > 1 && (int64_t)pl->n_cells_ext * ipow(T1, D) * ipow(fpc, D) > max_fine) fpc--;
+    DGS_REQUIRE((int64_t)pl->n_cells_ext * ipow(T1, D) * ipow(fpc, D) <= (int64_t)1 << 26, DGS_ERR_UNSUPPORTED,
+                "cell grid too large for the tile hierarchy");
+    pl->T1 = T1; pl->fpc = fpc; pl->F = T1 * fpc;
+    pl->coarse_per_cell = (int)ipow(T1, D);
+    pl->fine_per_coarse = (int)ipow(fpc, D);
+    pl->n_coarse = pl->n_cells_ext * pl->coarse_per_cell;
+    pl->n_fine = pl->n_coarse * pl->fine_per_coarse;
+    return 0;
+}
+
+extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float* means_dev, const float* conics_dev, const float* samples_dev,
+                              int64_t P, int64_t N, int D, const float* bounds_host, float tau,
+                              void* geom_dev, size_t geom_bytes, dgs_plan_t* plan, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    DGS_REQUIRE(plan != nullptr, DGS_ERR_BAD_ARG, "plan is null");
+    DGS_REQUIRE(D >= 1 && D <= 3, DGS_ERR_UNSUPPORTED, "D must be 1, 2 or 3");
+    DGS_REQUIRE(P >= 0 && N >= 1, DGS_ERR_BAD_ARG, "need P >= 0 and N >= 1");
+    DGS_REQUIRE(P < ((int64_t)1 << 31) && N < ((int64_t)1 << 32), DGS_ERR_UNSUPPORTED, "P or N too large for 32-bit list entries");
+    const GeomLayout gl = geom_layout(P);
+    DGS_REQUIRE(geom_dev && geom_bytes >= gl.total, DGS_ERR_BUFFER_TOO_SMALL, "geometry scratch too small (dgs_geom_bytes)");
+    memset(plan, 0, sizeof(*plan));
+    plan->magic = DGS_PLAN_MAGIC; plan->abi = DGS_ABI_VERSION; plan->D = D; plan->P = P; plan->N = N;
+    plan->tau = tau > 0.f ? tau : DGS_DEFAULT_TAU;
+    plan->geom_bytes = gl.total;
+    uint8_t* g = (uint8_t*)geom_dev;
+    DgsDevHeader* hdr = (DgsDevHeader*)(g + gl.hdr);
+    int rc = dgs_launch_header_init(hdr, st);
+    if (rc) return rc;
+    if (bounds_host) {
+        DGS_CUDA(cudaMemcpyAsync(hdr->lo, bounds_host, sizeof(float) * D, cudaMemcpyHostToDevice, st));
+        DGS_CUDA(cudaMemcpyAsync(hdr->hi, bounds_host + D, sizeof(float) * D, cudaMemcpyHostToDevice, st));
+    } else {
+        rc = dgs_launch_bounds(samples_dev, N, D, hdr, st);
+        if (rc) return rc;
+    }
+    rc = dgs_launch_crec(means_dev, conics_dev, P, D, plan->tau + DGS_TAU_MAX_EXTRA, hdr, (DgsCullRec*)(g + gl.crec), st);
+    if (rc) return rc;
+    DgsDevHeader h;
+    DGS_CUDA(cudaMemcpyAsync(&h, hdr, sizeof(h), cudaMemcpyDeviceToHost, st));
+    DGS_CUDA(cudaStreamSynchronize(st));
+    // tile_grid = ceil((max - min + 1e-6f) / 0.51f)   (sample_points.cu:72-73; ATen divides a CUDA
+    // tensor by a CPU scalar by multiplying with the fp32 reciprocal)
+    const float inv = 1.0f / DGS_CELL;
+    int64_t blocks = 1;
+    for (int d = 0; d < D; d++) {
+        plan->lo[d] = h.lo[d]; plan->hi[d] = h.hi[d];
+        DGS_REQUIRE(isfinite(h.lo[d]) && isfinite(h.hi[d]) && h.lo[d] <= h.hi[d], DGS_ERR_BAD_ARG, "sample bounds are not finite");
+        volatile float ext = (h.hi[d] - h.lo[d]) + 1e-6f;
+        volatile float q = ext * inv;
+        const int gd = (int)ceilf(q);
+        DGS_REQUIRE(gd >= 1 && gd < (1 << 20), DGS_ERR_UNSUPPORTED, "cell grid out of range");
+        plan->grid[d] = gd;
+        blocks *= gd;
+    }
+    DGS_REQUIRE(blocks < ((int64_t)1 << 24), DGS_ERR_UNSUPPORTED, "too many cells");
+    plan->blocks = (int)blocks;
+    plan->n_ranges = plan->blocks + 1;
+    plan->sort_bits = (int)higher_msb((uint32_t)plan->blocks);
+    int64_t ext_cells = plan->grid[0];
+    if (D > 1) ext_cells += (int64_t)plan->grid[1] * plan->grid[0];
+    if (D > 2) ext_cells += (int64_t)plan->grid[2] * plan->grid[1] * plan->grid[0];
+    plan->n_cells_ext = (int)(ext_cells + 1);
+    plan->mean_extent = h.extent_cnt ? (float)(h.extent_sum / (double)h.extent_cnt) : 0.f;
+    plan->exact_wrap = (h.flags & DGS_HDR_EXACT_WRAP) ? 1 : 0;
+    rc = choose_tiles(plan);
+    if (rc) return rc;
+    plan->ranges_bytes = (uint64_t)plan->blocks * 8 + 8;
+    sample_layout(plan);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// step 2: counts (Gaussian side) + the whole sample side
+// ---------------------------------------------------------------------------------------
+static int check_plan(const dgs_plan_t* pl) {
+    DGS_REQUIRE(pl && pl->magic == DGS_PLAN_MAGIC && pl->abi == DGS_ABI_VERSION, DGS_ERR_BAD_PLAN, "bad plan (magic/abi)");
+    DGS_REQUIRE(pl->D >= 1 && pl->D <= 3 && pl->n_coarse > 0 && pl->n_fine > 0, DGS_ERR_BAD_PLAN, "bad plan (fields)");
+    return 0;
+}
+
+extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_plan_t* plan, const float* means_dev, const float* covariances_dev,
+                                    const float* samples_dev, float* radii_dev, void* geom_dev, size_t geom_bytes,
+                                    void* sample_binning_dev, size_t sample_binning_bytes, void* sample_ranges_dev,
+                                    void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    const GeomLayout gl = geom_layout(plan->P);
+    DGS_REQUIRE(geom_dev && geom_bytes >= gl.total, DGS_ERR_BUFFER_TOO_SMALL, "geometry scratch too small");
+    DGS_REQUIRE(sample_binning_dev && sample_binning_bytes >= plan->sample_binning_bytes, DGS_ERR_BUFFER_TOO_SMALL,
+                "sample binning buffer too small (plan->sample_binning_bytes)");
+    uint8_t* g = (uint8_t*)geom_dev;
+    uint8_t* sb = (uint8_t*)sample_binning_dev;
+    DgsDevHeader* hdr = (DgsDevHeader*)(g + gl.hdr);
+    uint32_t* touched = (uint32_t*)(g + gl.touched);
+    uint32_t* offsets = (uint32_t*)(g + gl.offsets);
+    uint32_t* n1 = (uint32_t*)(g + gl.n1);
+    uint32_t* n1_off = (uint32_t*)(g + gl.n1_off);
+    void* gscan = g + gl.scan_tmp;
+    const DgsCullRec* crec = (const DgsCullRec*)(g + gl.crec);
+    const int64_t P = plan->P, N = plan->N;
+    const int D = plan->D;
+
+    // --- Gaussian side: radius / tiles_touched / inclusive scan ---
+    rc = dgs_launch_gauss_preprocess(means_dev, covariances_dev, P, D, plan, radii_dev, touched, st);
+    if (rc) return rc;
+    rc = dgs_inclusive_scan_u32(touched, offsets, P, gscan, &hdr->num_rendered, st);
+    if (rc) return rc;
+
+    // --- sample side ---
+    const SampleTmp tl = sample_tmp_layout(plan);
+    uint8_t* stmp = sb + plan->s_tmp_off;
+    PublicArrays pa = public_arrays(sb, (uint64_t)N);
+    uint32_t* fine_start = (uint32_t*)(sb + plan->s_fine_start_off);
+    uint32_t* fine_ids = (uint32_t*)(sb + plan->s_fine_ids_off);
+    float* fine_xyz = (float*)(sb + plan->s_fine_xyz_off);
+    float* fine_aabb = (float*)(sb + plan->s_fine_aabb_off);
+    float* coarse_aabb = (float*)(sb + plan->s_coarse_aabb_off);
+    uint32_t* tile_of = (uint32_t*)(stmp + tl.tile_of);
+    uint32_t* rank_of = (uint32_t*)(stmp + tl.rank_of);
+    DGS_CUDA(cudaMemsetAsync(fine_start, 0, ((size_t)plan->n_fine + 1) * 4, st));
+    rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr, st);
+    if (rc) return rc;
+    rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
+    if (rc) return rc;
+    rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
+    if (rc) return rc;
+    rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
+    if (rc) return rc;
+    // public sorted sample list: stable sort on the cell bits == sort on bits [0, 32+bit)
+    rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(stmp + tl.alt_keys),
+                            (uint32_t*)(stmp + tl.alt_vals), N, 32, 32 + plan->sort_bits, stmp + tl.sort_tmp, st);
+    if (rc) return rc;
+    rc = dgs_launch_ranges(pa.keys, N, sample_ranges_dev, plan->n_ranges, st);
+    if (rc) return rc;
+
+    // --- size of the coarse-tile lists ---
+    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, plan, coarse_aabb, n1, nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
+    rc = dgs_exclusive_scan_u32(n1, n1_off, P, gscan, (uint32_t*)&hdr->n_l1, st);
+    if (rc) return rc;
+
+    DgsDevHeader h;
+    DGS_CUDA(cudaMemcpyAsync(&h, hdr, sizeof(h), cudaMemcpyDeviceToHost, st));
+    DGS_CUDA(cudaStreamSynchronize(st));
+    DGS_REQUIRE(!(h.flags & DGS_HDR_OUTSIDE), DGS_ERR_SAMPLE_OUTSIDE_BOUNDS, "a sample lies outside the given bounds (or is NaN)");
+    plan->num_rendered = h.num_rendered;
+    plan->n_l1 = (uint64_t)(uint32_t)h.n_l1;
+    gauss_layout(plan);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// step 3: Gaussian lists
+// ---------------------------------------------------------------------------------------
+extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const dgs_plan_t* plan, const float* means_dev, const float* radii_dev,
+                                  void* geom_dev, size_t geom_bytes, void* binning_dev, size_t binning_bytes,
+                                  void* sample_binning_dev, size_t sample_binning_bytes, void* ranges_dev, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    const GeomLayout gl = geom_layout(plan->P);
+    DGS_REQUIRE(geom_dev && geom_bytes >= gl.total, DGS_ERR_BUFFER_TOO_SMALL, "geometry scratch too small");
+    DGS_REQUIRE(binning_dev && binning_bytes >= plan->binning_bytes, DGS_ERR_BUFFER_TOO_SMALL,
+                "binning buffer too small (plan->binning_bytes)");
+    DGS_REQUIRE(sample_binning_dev && sample_binning_bytes >= plan->sample_binning_bytes, DGS_ERR_BUFFER_TOO_SMALL,
+                "sample binning buffer too small");
+    uint8_t* g = (uint8_t*)geom_dev;
+    uint8_t* gb = (uint8_t*)binning_dev;
+    uint8_t* sb = (uint8_t*)sample_binning_dev;
+    const int64_t P = plan->P;
+    const uint64_t L = plan->num_rendered;
+    const GaussTmp tl = gauss_tmp_layout(plan);
+    uint8_t* tmp = gb + plan->g_sort_tmp_off;
+    PublicArrays pa = public_arrays(gb, L);
+    const uint32_t* offsets = (const uint32_t*)(g + gl.offsets);
+    const uint32_t* n1_off = (const uint32_t*)(g + gl.n1_off);
+
+    rc = dgs_launch_duplicate(means_dev, radii_dev, offsets, P, plan->D, plan, pa.keys_unsorted, pa.list_unsorted, st);
+    if (rc) return rc;
+    rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(tmp + tl.pub_alt_k),
+                            (uint32_t*)(tmp + tl.pub_alt_v), (int64_t)L, 32, 32 + plan->sort_bits, tmp + tl.pub_sort_tmp, st);
+    if (rc) return rc;
+    rc = dgs_launch_ranges(pa.keys, (int64_t)L, ranges_dev, plan->n_ranges, st);
+    if (rc) return rc;
+
+    // internal: cull records move next to the lists; coarse-tile lists
+    DgsCullRec* crec = (DgsCullRec*)(gb + plan->g_crec_off);
+    if (P > 0) DGS_CUDA(cudaMemcpyAsync(crec, g + gl.crec, (size_t)P * sizeof(DgsCullRec), cudaMemcpyDeviceToDevice, st));
+    uint32_t* l1_start = (uint32_t*)(gb + plan->g_l1_start_off);
+    uint32_t* l1_ids = (uint32_t*)(gb + plan->g_l1_ids_off);
+    uint32_t* keys_u = (uint32_t*)(tmp + tl.l1_keys_u);
+    uint32_t* vals_u = (uint32_t*)(tmp + tl.l1_vals_u);
+    uint32_t* keys_s = (uint32_t*)(tmp + tl.l1_keys_s);
+    const float* coarse_aabb = (const float*)(sb + plan->s_coarse_aabb_off);
+    if (plan->n_l1 > 0) {
+        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, plan, coarse_aabb, nullptr, n1_off, keys_u, vals_u, st);
+        if (rc) return rc;
+        rc = dgs_sort_pairs_u32(keys_u, vals_u, keys_s, l1_ids, (uint32_t*)(tmp + tl.l1_alt_k), (uint32_t*)(tmp + tl.l1_alt_v),
+                                (int64_t)plan->n_l1, 0, ceil_log2((uint64_t)plan->n_coarse), tmp + tl.l1_sort_tmp, st);
+        if (rc) return rc;
+    }
+    rc = dgs_launch_l1_start(keys_s, (int64_t)plan->n_l1, plan->n_coarse, l1_start, st);
+    if (rc) return rc;
+    DGS_CUDA(cudaMemcpyAsync(gb + plan->g_plan_off, plan, sizeof(*plan), cudaMemcpyHostToDevice, st));
+    DGS_CUDA(cudaMemcpyAsync(sb + plan->s_plan_off, plan, sizeof(*plan), cudaMemcpyHostToDevice, st));
+    return 0;
+}
+
+extern "C" __attribute__((visibility("default"))) int dgs_plan_from_buffer(const void* binning_dev, size_t binning_bytes, uint32_t num_rendered,
+                                    dgs_plan_t* plan, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t off = dgs_public_bytes(num_rendered);
+    DGS_REQUIRE(binning_dev && plan && binning_bytes >= off + sizeof(dgs_plan_t), DGS_ERR_BUFFER_TOO_SMALL, "binning buffer too small");
+    DGS_CUDA(cudaMemcpyAsync(plan, (const uint8_t*)binning_dev + off, sizeof(*plan), cudaMemcpyDeviceToHost, st));
+    DGS_CUDA(cudaStreamSynchronize(st));
+    return check_plan(plan);
+}
+
+// ---------------------------------------------------------------------------------------
+// forward / backward
+// ---------------------------------------------------------------------------------------
+extern "C" __attribute__((visibility("default"))) int dgs_sample_forward(const dgs_plan_t* plan, int fn, int C, const float* means_dev, const float* values_dev,
+                                  const float* conics_dev, const float* samples_dev, const void* binning_dev,
+                                  const void* sample_binning_dev, const void* ranges_dev, const void* sample_ranges_dev,
+                                  float* out_dev, void* stream) {
+    (void)samples_dev; (void)sample_ranges_dev;
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    DGS_REQUIRE(fn >= 0 && fn <= 3 && C >= 1, DGS_ERR_BAD_ARG, "fn must be 0..3 and C >= 1");
+    return dgs_launch_forward(plan, fn, C, means_dev, values_dev, conics_dev, (const uint8_t*)binning_dev,
+                              (const uint8_t*)sample_binning_dev, ranges_dev, out_dev, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" __attribute__((visibility("default"))) int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C, const float* means_dev, const float* values_dev,
+                                   const float* conics_dev, const float* samples_dev, const float* dout_dev,
+                                   const void* binning_dev, const void* sample_binning_dev, const void* ranges_dev,
+                                   const void* sample_ranges_dev, float* dmeans_dev, float* dvalues_dev, float* dconics_dev,
+                                   void* stream) {
+    (void)samples_dev; (void)sample_ranges_dev;
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    DGS_REQUIRE(fn >= 0 && fn <= 3 && C >= 1, DGS_ERR_BAD_ARG, "fn must be 0..3 and C >= 1");
+    return dgs_launch_backward(plan, fn, C, means_dev, values_dev, conics_dev, dout_dev, (const uint8_t*)binning_dev,
+                               (const uint8_t*)sample_binning_dev, ranges_dev, dmeans_dev, dvalues_dev, dconics_dev,
+                               (cudaStream_t)stream);
+}
+
+extern "C" __attribute__((visibility("default"))) int dgs_count_pairs(const dgs_plan_t* plan, int fn, const void* binning_dev, const void* sample_binning_dev,
+                               unsigned long long* counter_dev, void* stream) {
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    return dgs_launch_forward(plan, fn, 1, nullptr, nullptr, nullptr, (const uint8_t*)binning_dev,
+                              (const uint8_t*)sample_binning_dev, nullptr, nullptr, counter_dev, (cudaStream_t)stream);
+}
+
+extern "C" __attribute__((visibility("default"))) size_t dgs_plan_sizeof(void) { return sizeof(dgs_plan_t); }

@@ -1,0 +1,93 @@
+// dgs_common.cuh — shared declarations of libdgs_b200 (sm_100a only).
+//
+// Constants come from the reference's cuda_sampler/config.h:18-20 (BLOCK_SIZE 0.51f,
+// TORUS defined, FLOAT = float) and define results, so they are hard-wired here.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/dgs_b200.h"
+
+#define DGS_CELL 0.51f           // config.h:18
+#define DGS_THREADS 256          // CTA size of every kernel in this library
+#define DGS_DEFAULT_TAU 16.0f    // gaussian; higher orders add DGS_TAU_STEP per order
+#define DGS_TAU_STEP 2.0f
+#define DGS_TAU_MAX_EXTRA 6.0f   // tile lists are built for tau + 3*step
+
+// --- error plumbing ------------------------------------------------------------------
+void dgs_set_error(const char* fmt, ...);
+#define DGS_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            dgs_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return (int)e_;                                                              \
+        }                                                                                \
+    } while (0)
+#define DGS_LAUNCH_CHECK() DGS_CUDA(cudaGetLastError())
+#define DGS_REQUIRE(cond, code, msg)                                                     \
+    do {                                                                                 \
+        if (!(cond)) { dgs_set_error("%s:%d: %s", __FILE__, __LINE__, msg); return code; } \
+    } while (0)
+
+static inline size_t dgs_a128(size_t x) { return (x + 127) & ~(size_t)127; }
+static inline int dgs_cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// --- per-Gaussian cull record (32 B) -------------------------------------------------
+// mu: mean at preprocess time; R: half width of the box around the ellipsoid
+// power >= -tau_max along each axis; rs2: squared radius of the sphere around it;
+// flags bit0: never cull (far from the sample box, or conic not positive definite).
+struct __align__(16) DgsCullRec {
+    float mu[3];
+    float R[3];
+    float rs2;
+    uint32_t flags;
+};
+#define DGS_CREC_ALWAYS 1u
+
+// --- device-side header written by the step-1/2 kernels and copied back to the host ---
+struct DgsDevHeader {
+    float lo[3];
+    float hi[3];
+    uint32_t lo_bits[3];   // ordered-int encodings used by the atomic min/max
+    uint32_t hi_bits[3];
+    uint32_t num_rendered;
+    uint32_t flags;        // bit0: exact wrap needed; bit1: a sample lies outside the bounds
+    unsigned long long n_l1;
+    double extent_sum;     // sum over Gaussians/axes of the cull half width (finite ones)
+    unsigned long long extent_cnt;
+    uint32_t pad[8];
+};
+#define DGS_HDR_EXACT_WRAP 1u
+#define DGS_HDR_OUTSIDE 2u
+
+// --- scan / sort primitives (dgs_scan_sort.cu) -----------------------------------------
+// Exclusive scan of n uint32 (in place allowed).  tmp: dgs_scan_tmp_bytes(n).  If total_out
+// != nullptr the grand total is written there (device pointer).
+size_t dgs_scan_tmp_bytes(int64_t n);
+int dgs_exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, void* tmp, uint32_t* total_out,
+                           cudaStream_t st);
+// inclusive variant (reference: cub::DeviceScan::InclusiveSum, sampler_impl.cu:253)
+int dgs_inclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, void* tmp, uint32_t* total_out,
+                           cudaStream_t st);
+
+// Stable LSD radix sort of (key,val) pairs on key bits [begin_bit, end_bit), 8 bits per pass.
+// KEY64: keys are uint64 (public lists, reference cub::DeviceRadixSort::SortPairs on
+// [0, 32+bit), sampler_impl.cu:279-283; the low 32 bits are already ascending so only the
+// cell bits are sorted).  Result always lands in keys_out/vals_out; keys_in/vals_in are
+// preserved when passes == 1, otherwise alt buffers are used as ping-pong.
+size_t dgs_sort_tmp_bytes(int64_t n);
+int dgs_sort_pairs_u64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                       uint64_t* keys_alt, uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit, void* tmp,
+                       cudaStream_t st);
+int dgs_sort_pairs_u32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out,
+                       uint32_t* keys_alt, uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit, void* tmp,
+                       cudaStream_t st);
+
+// --- kernels launched from dgs_api.cu ---------------------------------------------------
+int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
+                       const float* conics, const uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
+                       float* out, unsigned long long* pair_counter, cudaStream_t st);
+int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
+                        const float* conics, const float* dout, const uint8_t* gbuf, const uint8_t* sbuf,
+                        const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st);

@@ -1,0 +1,137 @@
+// dgs_field.cuh — per-pair field arithmetic shared by the accumulation kernels.
+//
+// What is evaluated (reference file:line):
+//   displacement + torus wrap ........ cuda_sampler/forward.cu:147-158
+//   gaussian / derivative / laplacian (full Hessian) / third ... forward.cu:168-275
+//   the matching backward bodies ..... cuda_sampler/backward.cu:108-416
+// The reference hard-codes D==1 and D==2; here the general-D closed forms are used
+//   a = C X,  G = exp(-X.a/2),  H1_i = a_i,  H2_ij = a_i a_j - C_ij,
+//   H3_ijk = C_ij a_k + C_ik a_j + C_jk a_i - a_i a_j a_k,
+// which reduce to the reference's expressions for D <= 2 and define D == 3 (no reference arm).
+// Symmetric tensors are kept as their unique components (i<=j<=k) and expanded on store.
+#pragma once
+#include "dgs_common.cuh"
+
+#define DGS_HD __host__ __device__ __forceinline__
+
+// packed index of C_ij, i<=j, row-major upper triangle ([xx,xy,yy] / [xx,xy,xz,yy,yz,zz])
+DGS_HD constexpr int dgs_tri(int D, int i, int j) { return i * D - (i * (i - 1)) / 2 + (j - i); }
+DGS_HD constexpr int dgs_tri_sym(int D, int i, int j) { return i <= j ? dgs_tri(D, i, j) : dgs_tri(D, j, i); }
+// number of unique components of a symmetric order-n tensor in D dims
+DGS_HD constexpr int dgs_nuniq(int D, int n) {
+    return n == 0 ? 1 : n == 1 ? D : n == 2 ? D * (D + 1) / 2 : D * (D + 1) * (D + 2) / 6;
+}
+DGS_HD constexpr int dgs_ipow(int D, int n) { return n == 0 ? 1 : D * dgs_ipow(D, n - 1); }
+// index of the sorted triple i<=j<=k in lexicographic enumeration
+DGS_HD constexpr int dgs_u3(int D, int i, int j, int k) {
+    int u = 0;
+    for (int a = 0; a < D; a++)
+        for (int b = a; b < D; b++)
+            for (int c = b; c < D; c++) {
+                if (a == i && b == j && c == k) return u;
+                u++;
+            }
+    return u;
+}
+DGS_HD constexpr int dgs_u3_any(int D, int i, int j, int k) {
+    // sort three indices
+    int a = i, b = j, c = k, t = 0;
+    if (a > b) { t = a; a = b; b = t; }
+    if (b > c) { t = b; b = c; c = t; }
+    if (a > b) { t = a; a = b; b = t; }
+    return dgs_u3(D, a, b, c);
+}
+// unique-component index of full tensor index alpha (row-major digits, most significant first)
+DGS_HD constexpr int dgs_uniq_of(int D, int order, int alpha) {
+    if (order == 0) return 0;
+    if (order == 1) return alpha;
+    if (order == 2) return dgs_tri_sym(D, alpha / D, alpha % D);
+    return dgs_u3_any(D, alpha / (D * D), (alpha / D) % D, alpha % D);
+}
+
+template <bool EXACT>
+__device__ __forceinline__ float dgs_wrap(float X) {
+    if (EXACT) {
+        // forward.cu:150-156, literally (fmod in double; |X| >= 2 keeps the reference's quirk)
+        if (fabsf(X) > 1.0f) {
+            const double m = fmod((double)X, 2.0);
+            X = (float)(X >= 0.f ? m - 2.0 : m + 2.0);
+        }
+        return X;
+    } else {
+        // |X| < 2 is guaranteed by the plan: fmod(X,2) == X there
+        return X > 1.0f ? X - 2.0f : (X < -1.0f ? X + 2.0f : X);
+    }
+}
+
+// Geometry of one (Gaussian, sample) pair.  con: packed conic (real, unscaled).
+template <int D, int FN, bool EXACT, bool NEED_A = false>
+struct DgsPair {
+    float X[D];
+    float a[D];   // a = C X (valid for FN > 0, and always for D == 3 / D == 1 general path)
+    float G;      // exp(power), 0 where the reference skips the pair (power > 0)
+
+    __device__ __forceinline__ void eval(const float* x, const float* mu, const float* con) {
+#pragma unroll
+        for (int d = 0; d < D; d++) X[d] = dgs_wrap<EXACT>(mu[d] - x[d]);
+        float power;
+        if (D == 1) {
+            a[0] = con[0] * X[0];
+            power = -0.5f * a[0] * X[0];
+        } else if (D == 2) {
+            // same association as forward.cu:177 / :194-196 after nvcc's contraction
+            const float x1 = con[0] * X[0];
+            const float x2 = con[2] * X[1];
+            const float s = fmaf(x1, X[0], x2 * X[1]);
+            const float t = (con[1] * X[0]) * X[1];
+            power = fmaf(s, -0.5f, -t);
+            if (FN > 0 || NEED_A) {
+                a[0] = fmaf(con[1], X[1], x1);
+                a[1] = fmaf(con[1], X[0], x2);
+            }
+        } else {
+            float q = 0.f;
+#pragma unroll
+            for (int i = 0; i < D; i++) {
+                float s = 0.f;
+#pragma unroll
+                for (int j = 0; j < D; j++) s = fmaf(con[dgs_tri_sym(D, i, j)], X[j], s);
+                a[i] = s;
+                q = fmaf(s, X[i], q);
+            }
+            power = -0.5f * q;
+        }
+        const float e = __expf(power);
+        G = power > 0.0f ? 0.0f : e;
+    }
+
+    // unique components of the order-FN Hermite-like tensor H (out = sum v G H)
+    __device__ __forceinline__ void hermite(const float* con, float* H) const {
+        if (FN == 0) {
+            H[0] = 1.f;
+        } else if (FN == 1) {
+#pragma unroll
+            for (int i = 0; i < D; i++) H[i] = a[i];
+        } else if (FN == 2) {
+#pragma unroll
+            for (int i = 0; i < D; i++)
+#pragma unroll
+                for (int j = i; j < D; j++) H[dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
+        } else {
+            int u = 0;
+#pragma unroll
+            for (int i = 0; i < D; i++)
+#pragma unroll
+                for (int j = i; j < D; j++)
+#pragma unroll
+                    for (int k = j; k < D; k++) {
+                        const float cij = con[dgs_tri(D, i, j)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, j, k)];
+                        float h = cij * a[k];
+                        h = fmaf(cik, a[j], h);
+                        h = fmaf(cjk, a[i], h);
+                        h = fmaf(-(a[i] * a[j]), a[k], h);
+                        H[u++] = h;
+                    }
+        }
+    }
+};

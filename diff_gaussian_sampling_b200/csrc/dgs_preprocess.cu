@@ -1,0 +1,588 @@
+// dgs_preprocess.cu — binning kernels (HBM-bound integer/byte work).
+//
+// Public products, bit-exact with the reference:
+//   radii, tiles_touched ......... preprocessCUDA          cuda_sampler/forward.cu:24-83
+//   keys_unsorted / vals ......... duplicateWithKeys       cuda_sampler/sampler_impl.cu:54-129
+//   sample keys .................. sampleWithKeys          cuda_sampler/sampler_impl.cu:155-189
+//   ranges / sample_ranges ....... identifyTileRanges      cuda_sampler/sampler_impl.cu:134-151
+//   bounds / tile_grid ........... torch ops               sample_points.cu:70-74
+// Internal products (no reference counterpart): samples re-ordered by fine tile with their
+// coordinates packed SoA, per-tile bounding boxes, per-Gaussian cull records and the
+// coarse-tile Gaussian lists the accumulation kernels stream.
+//
+// One thread per Gaussian / per sample, 256-thread CTAs, coalesced SoA reads; unlike the
+// reference no kernel touches the device heap (forward.cu:63-64, sampler_impl.cu:72-73,167).
+#include "dgs_math.cuh"
+#include "dgs_preprocess.cuh"
+
+// ------------------------------------------------------------------------------------
+// bounds: samples.min(0) / samples.max(0)            (sample_points.cu:70-71)
+// ------------------------------------------------------------------------------------
+__global__ void dgs_header_init_kernel(DgsDevHeader* h) {
+    if (threadIdx.x == 0) {
+        for (int d = 0; d < 3; d++) { h->lo_bits[d] = 0xffffffffu; h->hi_bits[d] = 0u; h->lo[d] = 0.f; h->hi[d] = 0.f; }
+        h->num_rendered = 0; h->flags = 0; h->n_l1 = 0; h->extent_sum = 0.0; h->extent_cnt = 0;
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_bounds_kernel(const float* __restrict__ samples, int64_t n_flat, DgsDevHeader* h) {
+    // gridDim.x is a multiple of 3, so the flat stride is a multiple of D and each thread
+    // stays on one axis; consecutive threads read consecutive floats.
+    const int64_t stride = (int64_t)gridDim.x * DGS_THREADS;
+    const int64_t t = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    const int axis = (int)(t % D);
+    float lo = INFINITY, hi = -INFINITY;
+    for (int64_t i = t; i < n_flat; i += stride) {
+        const float v = samples[i];
+        lo = fminf(lo, v);
+        hi = fmaxf(hi, v);
+    }
+    __shared__ uint32_t s_lo[3], s_hi[3];
+    if (threadIdx.x < 3) { s_lo[threadIdx.x] = 0xffffffffu; s_hi[threadIdx.x] = 0u; }
+    __syncthreads();
+    if (lo <= hi) {
+        atomicMin(&s_lo[axis], dgs_f2ord(lo));
+        atomicMax(&s_hi[axis], dgs_f2ord(hi));
+    }
+    __syncthreads();
+    if (threadIdx.x < D) {
+        atomicMin(&h->lo_bits[threadIdx.x], s_lo[threadIdx.x]);
+        atomicMax(&h->hi_bits[threadIdx.x], s_hi[threadIdx.x]);
+    }
+}
+
+__global__ void dgs_bounds_finalize_kernel(DgsDevHeader* h, int D) {
+    if (threadIdx.x < D) {
+        h->lo[threadIdx.x] = dgs_ord2f(h->lo_bits[threadIdx.x]);
+        h->hi[threadIdx.x] = dgs_ord2f(h->hi_bits[threadIdx.x]);
+    }
+}
+
+int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, cudaStream_t st) {
+    const int64_t n_flat = N * D;
+    int nb = dgs_cdiv(n_flat, (int64_t)DGS_THREADS * 8);
+    nb = nb < 3 ? 3 : (nb > 148 * 12 ? 148 * 12 : ((nb + 2) / 3) * 3);
+    if (D == 1) dgs_bounds_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
+    else if (D == 2) dgs_bounds_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
+    else dgs_bounds_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
+    dgs_bounds_finalize_kernel<<<1, 32, 0, st>>>(h, D);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+int dgs_launch_header_init(DgsDevHeader* h, cudaStream_t st) {
+    dgs_header_init_kernel<<<1, 32, 0, st>>>(h);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// per-Gaussian cull record: the axis-aligned box and the sphere around the ellipsoid
+// power >= -tau_max, from the conic the accumulation kernels evaluate (forward.cu:168-184).
+// ------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __restrict__ means, const float* __restrict__ conics,
+                                                               int64_t P, float tau_max, DgsDevHeader* __restrict__ h,
+                                                               DgsCullRec* __restrict__ crec) {
+    constexpr int T = D * (D + 1) / 2;
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    double ext = 0.0;
+    unsigned cnt = 0;
+    uint32_t hflags = 0;
+    if (i < P) {
+        DgsCullRec r;
+        float con[T];
+#pragma unroll
+        for (int k = 0; k < T; k++) con[k] = conics[i * T + k];
+        double var[3] = {0, 0, 0};   // diagonal of Sigma = conic^-1
+        double lmax = 0.0;           // largest eigenvalue of Sigma
+        bool pd = true;
+        if (D == 1) {
+            const double c = con[0];
+            pd = c > 0.0;
+            var[0] = 1.0 / c;
+            lmax = var[0];
+        } else if (D == 2) {
+            const double c0 = con[0], c1 = con[1], c2 = con[2];
+            const double det = c0 * c2 - c1 * c1;
+            pd = (c0 > 0.0) && (det > 0.0);
+            var[0] = c2 / det;
+            var[1] = c0 / det;
+            const double mid = 0.5 * (c0 + c2);
+            const double disc = mid * mid - det;
+            const double lmaxC = mid + sqrt(disc > 0.0 ? disc : 0.0);
+            lmax = lmaxC / det;   // 1 / lambda_min(conic)
+        } else {
+            const double a = con[0], b = con[1], c = con[2], d = con[3], e = con[4], f = con[5];
+            const double A = d * f - e * e, B = c * e - b * f, Cc = b * e - c * d;
+            const double det = a * A + b * B + c * Cc;
+            const double m2 = a * d - b * b;
+            pd = (a > 0.0) && (m2 > 0.0) && (det > 0.0);
+            const double inv = 1.0 / det;
+            float sig[6];
+            sig[0] = (float)(A * inv);
+            sig[1] = (float)(B * inv);
+            sig[2] = (float)(Cc * inv);
+            sig[3] = (float)((a * f - c * c) * inv);
+            sig[4] = (float)((b * c - a * e) * inv);
+            sig[5] = (float)(m2 * inv);
+            var[0] = A * inv; var[1] = (a * f - c * c) * inv; var[2] = m2 * inv;
+            double dummy;
+            lmax = dgs_lambda_max3(sig, &dummy) * (1.0 + 1e-5);
+        }
+        uint32_t flags = 0;
+        bool finite = pd && isfinite(lmax) && lmax > 0.0;
+#pragma unroll
+        for (int d = 0; d < D; d++) finite = finite && isfinite(var[d]) && var[d] > 0.0;
+#pragma unroll
+        for (int d = 0; d < 3; d++) { r.mu[d] = 0.f; r.R[d] = 0.f; }
+        r.rs2 = 0.f;
+        bool far = false;
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            const float m = means[i * D + d];
+            r.mu[d] = m;
+            const float reach = fmaxf(fabsf(m - h->lo[d]), fabsf(m - h->hi[d]));
+            if (!(reach < 1.999f)) far = true;   // |mean - sample| may reach 2: fmod wrap quirk
+        }
+        if (far) hflags |= DGS_HDR_EXACT_WRAP;
+        if (!finite || far) {
+            flags |= DGS_CREC_ALWAYS;
+        } else {
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const float R = (float)sqrt(2.0 * (double)tau_max * var[d]) * 1.0001f + 1e-6f;
+                r.R[d] = R;
+                ext += R;
+                cnt++;
+            }
+            const float rs = (float)sqrt(2.0 * (double)tau_max * lmax) * 1.0001f + 1e-6f;
+            r.rs2 = rs * rs;
+        }
+        r.flags = flags;
+        crec[i] = r;
+    }
+    // block reduction of the statistics
+    __shared__ double s_ext[DGS_THREADS / 32];
+    __shared__ unsigned s_cnt[DGS_THREADS / 32];
+    __shared__ uint32_t s_flags;
+    if (threadIdx.x == 0) s_flags = 0;
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ext += __shfl_xor_sync(0xffffffffu, ext, o);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    if (hflags) atomicOr(&s_flags, hflags);
+    if ((threadIdx.x & 31) == 0) { s_ext[threadIdx.x >> 5] = ext; s_cnt[threadIdx.x >> 5] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double e = 0; unsigned c = 0;
+        for (int w = 0; w < DGS_THREADS / 32; w++) { e += s_ext[w]; c += s_cnt[w]; }
+        if (c) { atomicAdd(&h->extent_sum, e); atomicAdd(&h->extent_cnt, (unsigned long long)c); }
+        if (s_flags) atomicOr(&h->flags, s_flags);
+    }
+}
+
+int dgs_launch_crec(const float* means, const float* conics, int64_t P, int D, float tau_max, DgsDevHeader* h,
+                    DgsCullRec* crec, cudaStream_t st) {
+    if (P <= 0) return 0;
+    const int nb = dgs_cdiv(P, DGS_THREADS);
+    if (D == 1) dgs_crec_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
+    else if (D == 2) dgs_crec_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
+    else dgs_crec_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// preprocessCUDA (forward.cu:24-83): radius, cell rect, tiles_touched.  Bit-exact.
+// ------------------------------------------------------------------------------------
+struct DgsGrid {
+    int g[3];
+    float off[3];
+    int n_ranges;
+};
+
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_gauss_preprocess_kernel(const float* __restrict__ means, const float* __restrict__ cov,
+                                                                           int64_t P, DgsGrid G, float* __restrict__ radii,
+                                                                           uint32_t* __restrict__ touched) {
+    constexpr int T = D * (D + 1) / 2;
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (i >= P) return;
+    float c[T], p[D];
+#pragma unroll
+    for (int k = 0; k < T; k++) c[k] = cov[i * T + k];
+#pragma unroll
+    for (int k = 0; k < D; k++) p[k] = means[i * D + k];
+    float r = 0.f, r_out = 0.f;
+    uint32_t t_out = 0;
+    if (dgs_radius<D>(c, &r)) {
+        int rmin[D], rmax[D];
+        dgs_rect<D>(p, r, G.off, rmin, rmax);
+        uint32_t t = 1;
+#pragma unroll
+        for (int d = D - 1; d >= 0; d--) {
+            const int span = rmax[d] - rmin[d];
+            t *= (uint32_t)(span < G.g[d] ? span : G.g[d]);
+        }
+        if (t != 0) { r_out = r; t_out = t; }
+    }
+    radii[i] = r_out;
+    touched[i] = t_out;
+}
+
+int dgs_launch_gauss_preprocess(const float* means, const float* cov, int64_t P, int D, const dgs_plan_t* plan,
+                                float* radii, uint32_t* touched, cudaStream_t st) {
+    if (P <= 0) return 0;
+    DgsGrid G;
+    for (int d = 0; d < 3; d++) { G.g[d] = plan->grid[d]; G.off[d] = plan->lo[d]; }
+    G.n_ranges = plan->n_ranges;
+    const int nb = dgs_cdiv(P, DGS_THREADS);
+    if (D == 1) dgs_gauss_preprocess_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, cov, P, G, radii, touched);
+    else if (D == 2) dgs_gauss_preprocess_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, cov, P, G, radii, touched);
+    else dgs_gauss_preprocess_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, cov, P, G, radii, touched);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// Visits every cell the reference's duplicateWithKeys emits for one Gaussian, in its
+// emission order (outermost = last axis; sampler_impl.cu:82-124): f(linear_cell_id).
+template <int D, typename Fn>
+__device__ __forceinline__ void dgs_for_each_cell(const float* p, float r, const DgsGrid& G, Fn f) {
+    int rmin[3] = {0, 0, 0}, rmax[3] = {1, 1, 1};
+    dgs_rect<D>(p, r, G.off, rmin, rmax);
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        if (rmax[d] - rmin[d] >= G.g[d]) { rmin[d] = 0; rmax[d] = G.g[d]; }   // :100-107 axis collapse
+    }
+    const int g0 = G.g[0], g1 = D > 1 ? G.g[1] : 1, g2 = D > 2 ? G.g[2] : 1;
+    for (int z = rmin[2]; z < rmax[2]; z++) {
+        const int cz = D > 2 ? dgs_wrap_cell(z, g2) * g1 * g0 : 0;
+        for (int y = rmin[1]; y < rmax[1]; y++) {
+            const int cy = D > 1 ? dgs_wrap_cell(y, g1) * g0 : 0;
+            for (int x = rmin[0]; x < rmax[0]; x++) f(dgs_wrap_cell(x, g0) + cy + cz);
+        }
+    }
+}
+
+// duplicateWithKeys (sampler_impl.cu:54-129).  offsets = inclusive scan of tiles_touched.
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_duplicate_kernel(const float* __restrict__ means, const float* __restrict__ radii,
+                                                                    const uint32_t* __restrict__ offsets, int64_t P, DgsGrid G,
+                                                                    uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (i >= P) return;
+    const float r = radii[i];
+    if (!(r > 0.f)) return;
+    float p[D];
+#pragma unroll
+    for (int k = 0; k < D; k++) p[k] = means[i * D + k];
+    uint32_t o = (i == 0) ? 0u : offsets[i - 1];
+    dgs_for_each_cell<D>(p, r, G, [&](int cell) {
+        uint64_t key = (uint64_t)(int64_t)cell;
+        key <<= 32;
+        key |= (uint32_t)i;
+        keys[o] = key;
+        vals[o] = (uint32_t)i;
+        o++;
+    });
+}
+
+int dgs_launch_duplicate(const float* means, const float* radii, const uint32_t* offsets, int64_t P, int D,
+                         const dgs_plan_t* plan, uint64_t* keys, uint32_t* vals, cudaStream_t st) {
+    if (P <= 0) return 0;
+    DgsGrid G;
+    for (int d = 0; d < 3; d++) { G.g[d] = plan->grid[d]; G.off[d] = plan->lo[d]; }
+    G.n_ranges = plan->n_ranges;
+    const int nb = dgs_cdiv(P, DGS_THREADS);
+    if (D == 1) dgs_duplicate_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, radii, offsets, P, G, keys, vals);
+    else if (D == 2) dgs_duplicate_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, radii, offsets, P, G, keys, vals);
+    else dgs_duplicate_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, radii, offsets, P, G, keys, vals);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// identifyTileRanges (sampler_impl.cu:134-151).  ranges pre-zeroed; ids >= n_ranges skipped
+// (the reference would write out of bounds there).
+__global__ void __launch_bounds__(DGS_THREADS) dgs_ranges_kernel(const uint64_t* __restrict__ keys, int64_t L, uint2* __restrict__ ranges,
+                                                                 int n_ranges) {
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (i >= L) return;
+    const uint32_t cur = (uint32_t)(keys[i] >> 32);
+    if (i == 0) {
+        if (cur < (uint32_t)n_ranges) ranges[cur].x = 0;
+    } else {
+        const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+        if (cur != prev) {
+            if (prev < (uint32_t)n_ranges) ranges[prev].y = (uint32_t)i;
+            if (cur < (uint32_t)n_ranges) ranges[cur].x = (uint32_t)i;
+        }
+    }
+    if (i == L - 1 && cur < (uint32_t)n_ranges) ranges[cur].y = (uint32_t)L;
+}
+
+int dgs_launch_ranges(const uint64_t* keys, int64_t L, void* ranges, int n_ranges, cudaStream_t st) {
+    if (L <= 0) return 0;
+    dgs_ranges_kernel<<<dgs_cdiv(L, DGS_THREADS), DGS_THREADS, 0, st>>>(keys, L, (uint2*)ranges, n_ranges);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// sample side
+// ------------------------------------------------------------------------------------
+struct DgsTiles {
+    int g[3];
+    float off[3];
+    float hi[3];
+    int F, T1, fpc, cpc, fpcD;
+};
+
+static DgsTiles make_tiles(const dgs_plan_t* plan) {
+    DgsTiles t;
+    for (int d = 0; d < 3; d++) { t.g[d] = plan->grid[d]; t.off[d] = plan->lo[d]; t.hi[d] = plan->hi[d]; }
+    t.F = plan->F; t.T1 = plan->T1; t.fpc = plan->fpc; t.cpc = plan->coarse_per_cell; t.fpcD = plan->fine_per_coarse;
+    return t;
+}
+
+// sampleWithKeys (sampler_impl.cu:155-189) + fine-tile id and rank of every sample.
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_sample_keys_kernel(const float* __restrict__ samples, int64_t N, DgsTiles G,
+                                                                      uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                                      uint32_t* __restrict__ tile_of, uint32_t* __restrict__ rank_of,
+                                                                      uint32_t* __restrict__ fine_cnt, DgsDevHeader* __restrict__ h) {
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    const bool valid = i < N;
+    uint32_t tile = 0xffffffffu;
+    if (valid) {
+        uint32_t c[3] = {0, 0, 0};
+        int f[3] = {0, 0, 0};
+        bool outside = false;
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            const float s = samples[i * D + d];
+            float q;
+            const int cd = dgs_sample_cell(s, G.off[d], G.g[d], &q);
+            c[d] = (uint32_t)cd;
+            f[d] = dgs_fine_coord(q, cd, G.F);
+            outside = outside || !(s >= G.off[d] && s <= G.hi[d]);
+        }
+        uint32_t cell = c[0];
+        if (D > 1) cell += c[1] * (uint32_t)G.g[0];
+        if (D > 2) cell += c[2] * (uint32_t)G.g[1] * (uint32_t)G.g[0];
+        uint64_t key = cell;
+        key <<= 32;
+        key |= (uint32_t)i;
+        keys[i] = key;
+        vals[i] = (uint32_t)i;
+        uint32_t csub = 0, fsub = 0;
+#pragma unroll
+        for (int d = D - 1; d >= 0; d--) {
+            csub = csub * (uint32_t)G.T1 + (uint32_t)(f[d] / G.fpc);
+            fsub = fsub * (uint32_t)G.fpc + (uint32_t)(f[d] % G.fpc);
+        }
+        tile = (cell * (uint32_t)G.cpc + csub) * (uint32_t)G.fpcD + fsub;
+        if (outside) atomicOr(&h->flags, DGS_HDR_OUTSIDE);
+    }
+    const uint32_t peers = __match_any_sync(0xffffffffu, tile);
+    if (valid) {
+        const int lane = threadIdx.x & 31;
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&fine_cnt[tile], (uint32_t)__popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        tile_of[i] = tile;
+        rank_of[i] = base + __popc(peers & ((1u << lane) - 1u));
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_fine_scatter_kernel(const float* __restrict__ samples, int64_t N,
+                                                                       const uint32_t* __restrict__ tile_of, const uint32_t* __restrict__ rank_of,
+                                                                       const uint32_t* __restrict__ fine_start,
+                                                                       uint32_t* __restrict__ fine_ids, float* __restrict__ fine_xyz) {
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (i >= N) return;
+    const uint32_t pos = fine_start[tile_of[i]] + rank_of[i];
+    fine_ids[pos] = (uint32_t)i;
+#pragma unroll
+    for (int d = 0; d < D; d++) fine_xyz[(int64_t)d * N + pos] = samples[i * D + d];
+}
+
+// One CTA per coarse tile, one warp per fine tile: bounding boxes of the samples actually in
+// each tile.  Box layout (8 floats): lo[3], hi[3], count (as int), unused.  Empty: lo=+inf, hi=-inf.
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float* __restrict__ fine_xyz, int64_t N,
+                                                                    const uint32_t* __restrict__ fine_start, int fpcD,
+                                                                    float* __restrict__ fine_aabb, float* __restrict__ coarse_aabb) {
+    __shared__ float s_lo[DGS_THREADS / 32][3], s_hi[DGS_THREADS / 32][3];
+    __shared__ uint32_t s_n[DGS_THREADS / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t coarse = blockIdx.x;
+    float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    uint32_t cn = 0;
+    for (int ft = w; ft < fpcD; ft += DGS_THREADS / 32) {
+        const int64_t tile = coarse * fpcD + ft;
+        const uint32_t s0 = fine_start[tile], s1 = fine_start[tile + 1];
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t j = s0 + lane; j < s1; j += 32) {
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const float v = fine_xyz[(int64_t)d * N + j];
+                lo[d] = fminf(lo[d], v);
+                hi[d] = fmaxf(hi[d], v);
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lo[d] = fminf(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+                hi[d] = fmaxf(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], o));
+            }
+            clo[d] = fminf(clo[d], lo[d]);
+            chi[d] = fmaxf(chi[d], hi[d]);
+        }
+        cn += s1 - s0;
+        if (lane == 0) {
+            float* o = fine_aabb + tile * 8;
+            o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2]; o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
+            o[6] = __int_as_float((int)(s1 - s0)); o[7] = 0.f;
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int d = 0; d < 3; d++) { s_lo[w][d] = clo[d]; s_hi[w][d] = chi[d]; }
+        s_n[w] = cn;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        uint32_t n = 0;
+        for (int k = 0; k < DGS_THREADS / 32; k++) {
+            for (int d = 0; d < 3; d++) { lo[d] = fminf(lo[d], s_lo[k][d]); hi[d] = fmaxf(hi[d], s_hi[k][d]); }
+            n += s_n[k];
+        }
+        float* o = coarse_aabb + coarse * 8;
+        o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2]; o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
+        o[6] = __int_as_float((int)n); o[7] = 0.f;
+    }
+}
+
+int dgs_launch_sample_keys(const float* samples, const dgs_plan_t* plan, uint64_t* keys, uint32_t* vals, uint32_t* tile_of,
+                           uint32_t* rank_of, uint32_t* fine_cnt, DgsDevHeader* h, cudaStream_t st) {
+    const int64_t N = plan->N;
+    if (N <= 0) return 0;
+    DgsTiles G = make_tiles(plan);
+    const int nb = dgs_cdiv(N, DGS_THREADS);
+    if (plan->D == 1) dgs_sample_keys_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
+    else if (plan->D == 2) dgs_sample_keys_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
+    else dgs_sample_keys_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const uint32_t* tile_of, const uint32_t* rank_of,
+                            const uint32_t* fine_start, uint32_t* fine_ids, float* fine_xyz, cudaStream_t st) {
+    const int64_t N = plan->N;
+    if (N <= 0) return 0;
+    const int nb = dgs_cdiv(N, DGS_THREADS);
+    if (plan->D == 1) dgs_fine_scatter_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, N, tile_of, rank_of, fine_start, fine_ids, fine_xyz);
+    else if (plan->D == 2) dgs_fine_scatter_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, N, tile_of, rank_of, fine_start, fine_ids, fine_xyz);
+    else dgs_fine_scatter_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, N, tile_of, rank_of, fine_start, fine_ids, fine_xyz);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
+                         float* coarse_aabb, cudaStream_t st) {
+    if (plan->n_coarse <= 0) return 0;
+    const int nb = plan->n_coarse;
+    if (plan->D == 1) dgs_tile_aabb_kernel<1><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
+    else if (plan->D == 2) dgs_tile_aabb_kernel<2><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
+    else dgs_tile_aabb_kernel<3><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// coarse-tile Gaussian lists: Gaussian g is listed in coarse tile t iff cell(t) is one of the
+// cells the reference lists g in (membership is part of the result) AND the box of the
+// samples actually in t can reach power >= -tau_max.  EMIT=false counts, EMIT=true writes
+// (tile, g) pairs in ascending g; a stable sort by tile then yields ascending-g lists.
+// ------------------------------------------------------------------------------------
+template <int D, bool EMIT>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __restrict__ means, const float* __restrict__ radii,
+                                                             const DgsCullRec* __restrict__ crec, int64_t P, DgsGrid G, int cpc,
+                                                             const float* __restrict__ coarse_aabb, uint32_t* __restrict__ n1,
+                                                             const uint32_t* __restrict__ n1_off, uint32_t* __restrict__ keys,
+                                                             uint32_t* __restrict__ vals) {
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (i >= P) return;
+    const float r = radii[i];
+    uint32_t cnt = 0;
+    if (r > 0.f) {
+        float p[D];
+#pragma unroll
+        for (int k = 0; k < D; k++) p[k] = means[i * D + k];
+        const DgsCullRec rec = crec[i];
+        uint32_t o = EMIT ? n1_off[i] : 0u;
+        dgs_for_each_cell<D>(p, r, G, [&](int cell) {
+            if (cell >= G.n_ranges) return;
+            const int64_t t0 = (int64_t)cell * cpc;
+            for (int t = 0; t < cpc; t++) {
+                const float4 a = __ldg((const float4*)(coarse_aabb + (t0 + t) * 8));
+                const float4 b = __ldg((const float4*)(coarse_aabb + (t0 + t) * 8) + 1);
+                const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
+                if (!(lo[0] <= hi[0])) continue;   // no samples in this tile
+                if (dgs_cull_pass<D>(rec, lo, hi, 1.0f, 1.0f)) {
+                    if (EMIT) { keys[o] = (uint32_t)(t0 + t); vals[o] = (uint32_t)i; o++; }
+                    cnt++;
+                }
+            }
+        });
+    }
+    if (!EMIT) n1[i] = cnt;
+}
+
+int dgs_launch_l1(bool emit, const float* means, const float* radii, const DgsCullRec* crec, const dgs_plan_t* plan,
+                  const float* coarse_aabb, uint32_t* n1, const uint32_t* n1_off, uint32_t* keys, uint32_t* vals, cudaStream_t st) {
+    const int64_t P = plan->P;
+    if (P <= 0) return 0;
+    DgsGrid G;
+    for (int d = 0; d < 3; d++) { G.g[d] = plan->grid[d]; G.off[d] = plan->lo[d]; }
+    G.n_ranges = plan->n_ranges;
+    const int nb = dgs_cdiv(P, DGS_THREADS);
+    const int cpc = plan->coarse_per_cell;
+#define L1_LAUNCH(DD)                                                                                                         \
+    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, coarse_aabb, n1, n1_off, keys, vals); \
+    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, coarse_aabb, n1, n1_off, keys, vals);
+    if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
+#undef L1_LAUNCH
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// start[t] = first index of tile t in the tile-sorted entry list, for every t in [0, n_tiles]
+__global__ void __launch_bounds__(DGS_THREADS) dgs_l1_start_kernel(const uint32_t* __restrict__ keys_sorted, int64_t n, int n_tiles,
+                                                                   uint32_t* __restrict__ start) {
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (n == 0) {
+        if (i <= n_tiles) start[i] = 0;
+        return;
+    }
+    if (i > n) return;
+    // boundary i sits between entry i-1 and entry i
+    const int64_t prev = (i == 0) ? -1 : (int64_t)keys_sorted[i - 1];
+    const int64_t cur = (i == n) ? (int64_t)n_tiles : (int64_t)keys_sorted[i];
+    for (int64_t t = prev + 1; t <= cur; t++) start[t] = (uint32_t)i;
+}
+
+int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uint32_t* start, cudaStream_t st) {
+    const int64_t work = n == 0 ? (int64_t)n_tiles + 1 : n + 1;
+    dgs_l1_start_kernel<<<dgs_cdiv(work, DGS_THREADS), DGS_THREADS, 0, st>>>(keys_sorted, n, n_tiles, start);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}

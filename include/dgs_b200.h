@@ -13,8 +13,9 @@
  *   - all floats are fp32, row-major, contiguous (reference: .contiguous().data<float>(),
  *     sample_points.cu:84-93);
  *   - `stream` is a cudaStream_t passed as void*; everything is enqueued on it.  Only
- *     dgs_preprocess_count / dgs_aggregate_count synchronise (they return data-dependent
- *     sizes to the host, like the reference's cudaMemcpy D2H at sampler_impl.cu:257);
+ *     dgs_plan_begin / dgs_preprocess_count / dgs_plan_from_buffer / dgs_aggregate_count
+ *     synchronise (they return data-dependent sizes to the host, like the reference's
+ *     cudaMemcpy D2H at sampler_impl.cu:257 and .item() at sample_points.cu:74);
  *   - return value 0 = ok, otherwise a cudaError_t or a DGS_ERR_* code;
  *     dgs_last_error() gives a thread-local message.
  *   - fn: 0 gaussian, 1 derivative, 2 laplacian (full Hessian), 3 third
@@ -30,117 +31,158 @@
 extern "C" {
 #endif
 
-#define DGS_ABI_VERSION 1
+#define DGS_ABI_VERSION 2
 #define DGS_ERR_BAD_ARG 10001
 #define DGS_ERR_UNSUPPORTED 10002
 #define DGS_ERR_BUFFER_TOO_SMALL 10003
 #define DGS_ERR_BAD_PLAN 10004
+#define DGS_ERR_SAMPLE_OUTSIDE_BOUNDS 10005
 
 #define DGS_FN_GAUSSIAN 0
 #define DGS_FN_DERIVATIVE 1
 #define DGS_FN_LAPLACIAN 2
 #define DGS_FN_THIRD 3
 
-#define DGS_NCAND 7 /* candidate tiles-per-cell-axis: 1,2,4,...,64 */
+#define DGS_PLAN_MAGIC 0x44475342u /* "DGSB" */
 
 /*
- * Binning plan.  Filled by dgs_preprocess_count (host copy) and stored verbatim in the
- * header of both binning buffers so that forward/backward need no host-side state
- * (the reference re-derives `blocks` with a host sync in every call,
- * sample_points.cu:120-124,170-174; this replaces that).
+ * Binning plan: everything the host needs to size buffers and launch kernels.
+ * Filled in three steps (dgs_plan_begin -> dgs_preprocess_count -> dgs_preprocess_bin)
+ * and stored verbatim at the start of the internal part of both binning buffers, so
+ * forward/backward can be called with nothing but the reference's arguments
+ * (dgs_plan_from_buffer recovers it).  The reference instead re-derives `blocks`
+ * with three torch reductions and a host sync in every forward and backward
+ * (sample_points.cu:120-124,170-174).
  */
 typedef struct dgs_plan {
     uint32_t magic;
+    int32_t  abi;
     int32_t  D;
+    int32_t  exact_wrap;       /* 1: some |mean - sample| may reach 2 -> fmod wrap (forward.cu:150-156) */
     int64_t  P;
     int64_t  N;
     int32_t  grid[3];          /* cells per axis (reference tile_grid)                 */
     int32_t  blocks;           /* prod(grid)                                           */
     float    lo[3];            /* sample min bound == grid_offset                      */
     float    hi[3];            /* sample max bound                                     */
+    int32_t  n_ranges;         /* blocks + 1  (sample_points.cu:76: blocks*8+8 bytes)  */
+    int32_t  sort_bits;        /* getHigherMsb(blocks), sampler_impl.cu:39-50,276      */
     uint32_t num_rendered;     /* Gaussian/cell duplicates (reference return value)    */
-    float    tau;              /* pairs with power < -tau are skipped                  */
-    int32_t  T;                /* tiles per cell axis (internal sub-grid)              */
-    int32_t  tiles_per_cell;   /* T^D                                                  */
-    int32_t  n_tiles;          /* blocks * T^D                                         */
-    int32_t  M;                /* micro-cells per tile axis (sample ordering only)     */
-    int32_t  micro_per_tile;   /* M^D                                                  */
-    int32_t  n_fine;           /* n_tiles * M^D                                        */
-    uint64_t cand_entries[DGS_NCAND]; /* exact tile-list sizes for T = 1<<i            */
-    uint64_t n_tile_entries;   /* cand_entries[log2 T]                                 */
-    uint64_t binning_bytes;        /* required size of binning_buffer                  */
-    uint64_t sample_binning_bytes; /* required size of sample_binning_buffer           */
-    uint64_t scratch_bytes;        /* required size of the phase-2 scratch             */
-    uint64_t ranges_bytes;         /* blocks*8 + 8 (sample_points.cu:76)               */
-    /* offsets of the internal arrays inside the two buffers (bytes from buffer start) */
-    uint64_t g_header_off, g_tile_off_off, g_tile_entries_off;
-    uint64_t s_header_off, s_fine_ids_off, s_fine_xyz_off, s_tile_samp_off, s_work_prefix_off, s_fine_cnt_off;
+    float    tau;              /* pairs with power < -tau may be skipped               */
+    /* internal two-level tile hierarchy under each reference cell */
+    int32_t  n_cells_ext;      /* number of linear cell ids a key can carry            */
+    int32_t  T1;               /* coarse tiles per cell axis                           */
+    int32_t  fpc;              /* fine tiles per coarse tile axis                      */
+    int32_t  F;                /* fine tiles per cell axis = T1*fpc                    */
+    int32_t  coarse_per_cell;  /* T1^D                                                 */
+    int32_t  fine_per_coarse;  /* fpc^D                                                */
+    int32_t  n_coarse;         /* n_cells_ext * T1^D                                   */
+    int32_t  n_fine;           /* n_coarse * fpc^D                                     */
+    uint64_t n_l1;             /* entries of the coarse-tile Gaussian lists            */
+    float    mean_extent;      /* mean tau-bbox half width (statistic used to pick T1) */
+    int32_t  reserved0;
+    /* buffer sizes */
+    uint64_t geom_bytes;           /* phase scratch (reference: GeometryState)         */
+    uint64_t binning_bytes;        /* binning_buffer (valid after dgs_preprocess_count)*/
+    uint64_t sample_binning_bytes; /* sample_binning_buffer (valid after plan_begin)   */
+    uint64_t ranges_bytes;         /* blocks*8 + 8                                     */
+    /* byte offsets of the internal arrays from the start of each buffer */
+    uint64_t g_plan_off, g_crec_off, g_l1_start_off, g_l1_ids_off, g_sort_tmp_off;
+    uint64_t s_plan_off, s_fine_start_off, s_fine_ids_off, s_fine_xyz_off, s_fine_aabb_off,
+             s_coarse_aabb_off, s_tmp_off;
     int32_t  reserved[8];
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
+size_t      dgs_plan_sizeof(void);   /* sizeof(dgs_plan_t) the library was built with */
 const char* dgs_last_error(void);
 
-/* Bytes of the phase-1 scratch ("geometry buffer", reference GeometryState,
- * sampler_impl.cu:191-198). */
-size_t dgs_geom_bytes(int64_t P, int D);
+/* Bytes of the preprocess scratch ("geometry buffer"; reference GeometryState,
+ * sampler_impl.cu:191-198 — radii live outside it here, as a caller tensor). */
+size_t dgs_geom_bytes(int64_t P, int64_t N, int D);
+
+/* Offset of the internal part (plan header first) inside a binning buffer that holds L
+ * list entries: the four public arrays [point_list u32 | point_list_unsorted u32 |
+ * point_list_keys u64 | point_list_keys_unsorted u64], each start rounded up to 128 B
+ * (reference BinningState::fromChunk / obtain, sampler_impl.cu:200-212, sampler_impl.h:25-61). */
+size_t dgs_public_bytes(uint64_t L);
 
 /*
- * Phase 1 of preprocess_gaussians (reference: PreprocessCUDA, sample_points.cu:37-98, up to
- * and including the D2H read of num_rendered, sampler_impl.cu:234-257):
- *   sample bounds + cell grid (sample_points.cu:70-74), per-Gaussian radius / cell rect /
- *   tiles_touched (forward.cu:24-83), inclusive scan (sampler_impl.cu:253).
- * bounds_host: NULL -> bounds are reduced from `samples` like the reference; otherwise
- *   lo[D] followed by hi[D] (multi-GPU: every rank bins with the global bounds).
- * tau <= 0 selects the default.  Synchronises `stream`; fills *plan.
+ * Step 1 of preprocess_gaussians (reference: sample_points.cu:70-77): sample bounds
+ * (samples.min(0)/max(0)), tile_grid = ceil((max-min+1e-6f)/0.51f), blocks; plus this
+ * library's per-Gaussian cull records (from means/conics) and the choice of the internal
+ * tile hierarchy.  bounds_host: NULL -> bounds are reduced from `samples` like the
+ * reference (one host sync); otherwise lo[D] followed by hi[D], which must contain every
+ * sample (multi-GPU: every rank bins with the global bounds).  tau <= 0 selects the default.
+ * Fills plan->{grid,blocks,lo,hi,n_ranges,sort_bits,T1,fpc,...,geom_bytes,
+ * sample_binning_bytes,ranges_bytes}.  Synchronises `stream`.
  */
-int dgs_preprocess_count(const float* means_dev, const float* covariances_dev, const float* conics_dev,
-                         const float* samples_dev, int64_t P, int64_t N, int D,
-                         const float* bounds_host, float tau,
+int dgs_plan_begin(const float* means_dev, const float* conics_dev, const float* samples_dev,
+                   int64_t P, int64_t N, int D, const float* bounds_host, float tau,
+                   void* geom_dev, size_t geom_bytes, dgs_plan_t* plan, void* stream);
+
+/*
+ * Step 2 (reference: sampler_impl.cu:234-257 and :294-327): per-Gaussian radius / cell rect /
+ * tiles_touched (forward.cu:24-83), inclusive scan (sampler_impl.cu:253), D2H of
+ * num_rendered (:257); the whole sample side: sampleWithKeys (:155-189), key sort (:316-320),
+ * identifyTileRanges (:323) into the four public arrays of sample_binning_dev and
+ * sample_ranges_dev (zero-filled by the caller, plan->ranges_bytes), followed by the internal
+ * fine-tile ordering of the samples and the tile bounding boxes; and the count of the
+ * coarse-tile list entries.  Fills plan->{num_rendered,n_l1,binning_bytes,exact_wrap,...}.
+ * Synchronises `stream`.
+ */
+int dgs_preprocess_count(dgs_plan_t* plan,
+                         const float* means_dev, const float* covariances_dev, const float* samples_dev,
                          float* radii_dev, void* geom_dev, size_t geom_bytes,
-                         dgs_plan_t* plan, void* stream);
+                         void* sample_binning_dev, size_t sample_binning_bytes,
+                         void* sample_ranges_dev, void* stream);
 
 /*
- * Phase 2 (reference: sampler_impl.cu:259-329): duplicateWithKeys, key sort, identifyTileRanges
- * for Gaussians and samples, bit-exact with the reference's four public arrays
- * [point_list | point_list_unsorted | point_list_keys | point_list_keys_unsorted]
- * (each 128-byte aligned from the buffer start, sampler_impl.cu:200-212), followed by this
- * library's internal tile structures.  ranges / sample_ranges must be zero-filled,
- * plan->ranges_bytes each (sample_points.cu:76-77).  Asynchronous.
+ * Step 3 (reference: sampler_impl.cu:259-292): duplicateWithKeys, key sort on bits
+ * [0, 32+sort_bits), identifyTileRanges — bit-exact with the reference's four public arrays —
+ * then the internal coarse-tile Gaussian lists.  ranges_dev zero-filled by the caller
+ * (sample_points.cu:76).  Asynchronous.
  */
-int dgs_preprocess_bin(const dgs_plan_t* plan,
-                       const float* means_dev, const float* conics_dev, const float* samples_dev,
-                       const float* radii_dev, void* geom_dev,
+int dgs_preprocess_bin(const dgs_plan_t* plan, const float* means_dev, const float* radii_dev,
+                       void* geom_dev, size_t geom_bytes,
                        void* binning_dev, size_t binning_bytes,
                        void* sample_binning_dev, size_t sample_binning_bytes,
-                       void* ranges_dev, void* sample_ranges_dev,
-                       void* scratch_dev, size_t scratch_bytes, void* stream);
+                       void* ranges_dev, void* stream);
+
+/* Recovers the plan stored inside binning_dev (L = num_rendered entries).  Synchronises. */
+int dgs_plan_from_buffer(const void* binning_dev, size_t binning_bytes, uint32_t num_rendered,
+                         dgs_plan_t* plan, void* stream);
 
 /*
  * sample_gaussians / _derivative / _laplacian / _third_derivative forward
  * (reference: SampleGaussians*CUDA, sample_points.cu:100-143,198-297; kernels forward.cu:87-275).
- * out_dev: (N, D^fn, C) fp32, zero-filled by the caller (sample_points.cu:215).
- * work_dev: 64 zero-filled bytes of device scratch (dynamic work counter).
+ * out_dev: (N, D^fn, C) fp32; every element is written (the reference zero-fills and
+ * accumulates, sample_points.cu:215).  Asynchronous.
  */
-int dgs_sample_forward(int fn, int64_t P, int64_t N, int D, int C,
+int dgs_sample_forward(const dgs_plan_t* plan, int fn, int C,
                        const float* means_dev, const float* values_dev, const float* conics_dev,
-                       const float* samples_dev, uint32_t num_rendered,
+                       const float* samples_dev,
                        const void* binning_dev, const void* sample_binning_dev,
                        const void* ranges_dev, const void* sample_ranges_dev,
-                       float* out_dev, void* work_dev, void* stream);
+                       float* out_dev, void* stream);
 
 /*
  * Backward of the above (reference: SampleGaussians*BackwardCUDA, sample_points.cu:145-196,
  * 299-372; kernels backward.cu:26-416).  dmeans (P,D), dvalues (P,C), dconics (P,D(D+1)/2)
- * zero-filled by the caller (sample_points.cu:165-167).
+ * zero-filled by the caller (sample_points.cu:165-167); results are accumulated into them.
  */
-int dgs_sample_backward(int fn, int64_t P, int64_t N, int D, int C,
+int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C,
                         const float* means_dev, const float* values_dev, const float* conics_dev,
-                        const float* samples_dev, uint32_t num_rendered, const float* dout_dev,
+                        const float* samples_dev, const float* dout_dev,
                         const void* binning_dev, const void* sample_binning_dev,
                         const void* ranges_dev, const void* sample_ranges_dev,
-                        float* dmeans_dev, float* dvalues_dev, float* dconics_dev,
-                        void* work_dev, void* stream);
+                        float* dmeans_dev, float* dvalues_dev, float* dconics_dev, void* stream);
+
+/* Pairs the forward/backward kernels evaluate for this plan (sum over fine tiles of
+ * samples x surviving Gaussians); debugging / roofline accounting.  counter_dev: one
+ * zero-filled uint64 on the device.  Asynchronous. */
+int dgs_count_pairs(const dgs_plan_t* plan, int fn, const void* binning_dev, const void* sample_binning_dev,
+                    unsigned long long* counter_dev, void* stream);
 
 #ifdef __cplusplus
 }
