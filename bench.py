@@ -1,0 +1,432 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the differentiable Gaussian-sampling hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
+
+One "step" = one pass of the hot path over one batch of synthetic input, as a PIGS training
+step drives it: preprocess (binning) -> sample_gaussians forward -> backward (+ one NCCL
+allreduce of the flat gradient buffer when N > 1).  metric = query points / second (fwd+bwd
+incl. binning), on BASELINE.json configs[1]: 2D, P = 1M Gaussians x 4096^2 = 16.7M points, C = 1.
+N > 1: weak scaling — every rank evaluates its own 16.7M-point slab of an N x 16.7M-point grid
+over the same domain, Gaussians replicated, all ranks binning with the global bounds.
+
+Prints ONE JSON line (rank 0).  `value`: inputs resident in HBM; `e2e`: the same step through
+the public Python API with pinned HOST buffers copied in every step and the gradients + loss
+copied back.  `roofline`: the dominant kernel (backward accumulation) against the FP32 issue
+peak measured live by an FFMA microbenchmark in the same process.  `cpu_baseline`: the dense
+PyTorch-CPU port of the formula (oracle/dense_torch.py) on a bounded sample of the workload.
+`--impl reference`: the unmodified reference CUDA extension (baseline/_ref) on a bounded sample
+(it needs ~20 min per step at full size); falls back to the CPU port when it cannot be loaded.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    # name: (D, P, n per axis, C)
+    "cfg1": (2, 10_000, 256, 1),
+    "cfg2": (2, 1_000_000, 4096, 1),
+    "cfg3": (3, 1_000_000, 256, 1),
+}
+METRIC = "fwd+bwd query points/sec at 1M Gaussians x 16.7M pts"
+UNIT = "points/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--fn", type=int, default=0, help="0 gaussian, 1 derivative, 2 laplacian, 3 third")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------
+# synthetic inputs: seeded numpy, identical on every rank
+# ---------------------------------------------------------------------------------------
+def make_inputs(workload, rank, world):
+    import cases
+    D, P, n, C = WORKLOADS[workload]
+    rng = np.random.default_rng(0)
+    m, v, cov, con = cases.make_gaussians(rng, P, D, C, cases.sigma_for(P, D))
+    # weak scaling: the global grid has world*n points along axis 0; rank r owns rows [r*n, (r+1)*n)
+    ax0 = np.linspace(-1.0, 1.0, n * world, dtype=np.float64)[rank * n:(rank + 1) * n]
+    ax = np.linspace(-1.0, 1.0, n, dtype=np.float64)
+    mesh = np.meshgrid(ax0, *([ax] * (D - 1)), indexing="ij")
+    s = np.stack([g.reshape(-1) for g in mesh], -1).astype(np.float32)
+    bounds = (np.full(D, -1.0, np.float32), np.full(D, 1.0, np.float32))
+    return dict(means=m, values=v, covariances=cov, conics=con, samples=np.ascontiguousarray(s)), bounds
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------
+def flops_per_pair(D, C, fn):
+    """FP32 flop per evaluated (Gaussian, point) pair, FMA = 2: forward and backward
+    of `gaussian`; higher orders add accumulate/coefficient flops (forward only counted for fn > 0)."""
+    fwd = (16 + 2 * C) if D == 2 else ((27 + 2 * C) if D == 3 else (8 + 2 * C))
+    bwd = (32 + 3 * C) if D == 2 else ((60 + 3 * C) if D == 3 else (14 + 3 * C))
+    if fn > 0:
+        fwd += 2 * (D ** fn) * C + [0, 2, 3, 6][fn] * D * D
+    return fwd, bwd
+
+
+def measure_peaks(torch, lib, _lib):
+    """FP32 FFMA and MUFU.EX2 peaks of this device, measured now (burst, kernel timed alone)."""
+    import ctypes
+    out = torch.zeros(4, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    res = {}
+    for which, key in ((0, "fp32_tflops"), (1, "ex2_tera_per_s")):
+        work = ctypes.c_double(0.0)
+        best = 0.0
+        for rep in range(5):
+            a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+            a.record()
+            _lib.check(lib.dgs_microbench(which, 4096, out.data_ptr(), ctypes.byref(work), st), "dgs_microbench")
+            b.record(); torch.cuda.synchronize()
+            best = max(best, work.value / (a.elapsed_time(b) * 1e-3) / 1e12)
+        res[key] = best
+    return res
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import diff_gaussian_sampling_b200 as dgs
+    from diff_gaussian_sampling_b200 import _lib
+    lib = _lib.load()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    D, P, n, C = WORKLOADS[args.workload]
+    fn = args.fn
+    host, bounds = make_inputs(args.workload, rank, world)
+    N = host["samples"].shape[0]
+    T = D * (D + 1) // 2
+    pinned = {k: torch.from_numpy(v).pin_memory() for k, v in host.items()}
+    devt = {k: v.to(dev) for k, v in pinned.items()}
+    gen = torch.Generator(device=dev).manual_seed(1 + rank)
+    shape = (N,) + (D,) * fn + (C,)
+    dout = torch.randn(shape, device=dev, generator=gen)
+    calls = [dgs._C.sample_gaussians, dgs._C.sample_gaussians_derivative, dgs._C.sample_gaussians_laplacian,
+             dgs._C.sample_gaussians_third_derivative]
+    bcalls = [dgs._C.sample_gaussians_backward, dgs._C.sample_gaussians_derivative_backward,
+              dgs._C.sample_gaussians_laplacian_backward, dgs._C.sample_gaussians_third_derivative_backward]
+    l2_flush = torch.empty(160 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    t_pre, t_fwd, t_bwd = [], [], []
+    state = {}
+
+    def step(t, timed=False):
+        """preprocess -> forward -> backward (-> allreduce); returns the flat gradient buffer and out."""
+        e = [ev() for _ in range(4)] if timed else None
+        if timed: e[0].record()
+        nr, gb, sb, rg, srg, radii = dgs._C.preprocess_gaussians(t["means"], t["values"], t["covariances"], t["conics"],
+                                                               t["samples"], False, bounds=bounds)
+        if timed: e[1].record()
+        out = calls[fn](t["means"], t["values"], t["conics"], t["samples"], nr, gb, sb, rg, srg, False)
+        if timed: e[2].record()
+        dm, dv, dc = bcalls[fn](t["means"], t["values"], t["conics"], t["samples"], nr, dout, gb, sb, rg, srg, False)
+        if timed: e[3].record()
+        flat = dm.view(-1)._base if dm._base is not None else None
+        if flat is None:
+            flat = torch.cat([dm.reshape(-1), dv.reshape(-1), dc.reshape(-1)])
+        if world > 1:
+            dist.all_reduce(flat)      # ONE NCCL allreduce of [dL_dmeans | dL_dvalues | dL_dconics] per backward
+        state.update(nr=nr, gb=gb, sb=sb)
+        if timed:
+            state.setdefault("events", []).append(e)
+        return flat, out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    launches0 = None
+    for _ in range(max(3, args.warmup)):
+        l2_flush.zero_()
+        step(devt)
+    barrier()
+    clocks = ClockSampler(local_rank); clocks.start()
+    launches0 = lib.dgs_launch_count()
+    # ---- device-resident timing: K steps, inputs already in HBM; L2 flushed between steps ----
+    tot_ms = 0.0
+    for _ in range(args.steps):
+        l2_flush.zero_()
+        barrier()
+        a, b = ev(), ev()
+        a.record()
+        step(devt, timed=True)
+        b.record()
+        barrier()
+        tot_ms += a.elapsed_time(b)
+    launches = lib.dgs_launch_count() - launches0
+    for e in state["events"]:
+        t_pre.append(e[0].elapsed_time(e[1])); t_fwd.append(e[1].elapsed_time(e[2])); t_bwd.append(e[2].elapsed_time(e[3]))
+    # ---- end to end: pinned host inputs -> H2D every step, gradients + loss -> D2H every step ----
+    e2e = None
+    if not args.no_e2e:
+        grads_host = torch.empty(P * (D + C + T), dtype=torch.float32).pin_memory()
+        loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            t = {k: v.to(dev, non_blocking=True) for k, v in pinned.items()}
+            flat, out = step(t)
+            grads_host.copy_(flat, non_blocking=True)
+            loss_host.copy_((out * dout).sum().reshape(1), non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        e2e_ms = 0.0
+        for _ in range(args.steps):
+            l2_flush.zero_()
+            barrier()
+            a, b = ev(), ev()
+            a.record()
+            e2e_step()
+            b.record()
+            barrier()
+            e2e_ms += a.elapsed_time(b)
+        h2d = sum(v.numel() * v.element_size() for v in pinned.values())
+        d2h = grads_host.numel() * 4 + 4
+        e2e = dict(ms=e2e_ms, h2d=h2d, d2h=d2h)
+    clk = clocks.stop()
+    return dict(tot_ms=tot_ms, t_pre=t_pre, t_fwd=t_fwd, t_bwd=t_bwd, e2e=e2e, clocks=clk, launches=launches,
+                N=N, P=P, D=D, C=C, fn=fn, state=state, dgs=dgs, lib=lib, _lib=_lib, bounds=bounds, host=host)
+
+
+# ---------------------------------------------------------------------------------------
+# baselines
+# ---------------------------------------------------------------------------------------
+def sub_grid(D, n_sub):
+    import cases
+    return cases.grid_samples(n_sub, D)
+
+
+def cpu_port_baseline(workload, n_sub, chunk=64):
+    """Dense PyTorch-CPU port (oracle/dense_torch.py) on an n_sub^D sub-grid of the same domain against
+    all P Gaussians; cost is linear in the number of points, so points/s carries over."""
+    import torch
+    from oracle import dense_torch
+    host, bounds = make_inputs(workload, 0, 1)
+    D = host["means"].shape[1]
+    s = sub_grid(D, n_sub)
+    cores = os.cpu_count() or 1
+    dt, _, _ = dense_torch.timed_fwd_bwd(host["means"], host["values"], host["covariances"], host["conics"], s,
+                                         bounds=bounds, chunk=chunk, threads=cores)
+    return dict(value=s.shape[0] / dt, unit=UNIT, cores=cores, kind="port",
+                sample=f"dense PyTorch fp32 fwd+bwd (autograd), all P Gaussians x {s.shape[0]} points "
+                       f"({n_sub}^{D} sub-grid of the domain), {dt:.1f} s; binning by the C oracle not timed",
+                seconds=dt)
+
+
+def run_reference(args, rank):
+    """The reference arm: the unmodified reference CUDA extension (it has no CPU implementation) from
+    baseline/_ref on a bounded sample; CPU port when it cannot be loaded."""
+    D, P, n, C = WORKLOADS[args.workload]
+    base = dict(metric=METRIC, unit=UNIT, impl="reference", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                config={"workload": f"{args.workload}: {D}D, P={P} Gaussians x {n}^{D} query grid, C={C}, "
+                                    "sample_gaussians preprocess+fwd+bwd"})
+    try:
+        import torch
+        import refload
+        ok = torch.cuda.is_available() and refload.available() and D <= 2
+    except Exception:  # noqa: BLE001
+        ok = False
+    if ok:
+        import torch
+        ref = refload.load()
+        refload.raise_malloc_heap(8 << 30)
+        host, _ = make_inputs(args.workload, 0, 1)
+        n_sub = 128 if P >= 1_000_000 else min(n, 256)
+        s = sub_grid(D, n_sub)
+        dev = torch.device("cuda:0")
+        t = {k: torch.from_numpy(v).to(dev) for k, v in host.items()}
+        ts = torch.from_numpy(s).to(dev)
+        dout = torch.randn(s.shape[0], C, device=dev)
+        ev = lambda: torch.cuda.Event(enable_timing=True)
+
+        def step():
+            nr, bb, sbb, rg, srg, radii = ref._C.preprocess_gaussians(t["means"], t["values"], t["covariances"],
+                                                                    t["conics"], ts, False)
+            out = ref._C.sample_gaussians(t["means"], t["values"], t["conics"], ts, nr, bb, sbb, rg, srg, False)
+            ref._C.sample_gaussians_backward(t["means"], t["values"], t["conics"], ts, nr, dout, bb, sbb, rg, srg, False)
+
+        steps = args.steps
+        warm = max(1, min(args.warmup, 3))
+        for _ in range(warm):
+            step()
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(steps):
+            step()
+        b.record(); torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / steps
+        val = s.shape[0] / (ms * 1e-3)
+        base.update(value=val, ms_per_step=ms,
+                    cpu_baseline=dict(value=val, unit=UNIT, cores=0, kind="reference",
+                                      sample=f"unmodified reference CUDA extension (baseline/_ref; the reference has no "
+                                             f"CPU path) on cuda:0, all P={P} Gaussians x {s.shape[0]} points "
+                                             f"({n_sub}^{D} sub-grid; the full grid needs ~20 min/step), "
+                                             f"{ms:.0f} ms/step"),
+                    e2e=dict(value=val, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+        return base
+    n_sub = 16 if P >= 1_000_000 else 32
+    cb = cpu_port_baseline(args.workload, n_sub)
+    base.update(value=cb["value"], ms_per_step=cb["seconds"] * 1e3, cpu_baseline=cb,
+                e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    return base
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps(run_reference(args, rank)), flush=True)
+        return 0
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    r = run_ours(args, rank, world, local_rank)
+    D, P, N, C, fn = r["D"], r["P"], r["N"], r["C"], r["fn"]
+    tot = torch.tensor([r["tot_ms"], r["e2e"]["ms"] if r["e2e"] else 0.0], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    tot_ms, e2e_ms = float(tot[0]), float(tot[1])
+    if rank == 0:
+        dgs, lib, _lib = r["dgs"], r["lib"], r["_lib"]
+        K = args.steps
+        pairs = dgs.count_pairs(r["state"]["gb"], r["state"]["sb"], r["state"]["nr"], fn)
+        peaks = measure_peaks(torch, lib, _lib)
+        f_fwd, f_bwd = flops_per_pair(D, C, fn)
+        med = statistics.median
+        bwd_ms, fwd_ms, pre_ms = med(r["t_bwd"]), med(r["t_fwd"]), med(r["t_pre"])
+        ach_bwd = pairs * f_bwd / (bwd_ms * 1e-3) / 1e12
+        ach_fwd = pairs * f_fwd / (fwd_ms * 1e-3) / 1e12
+        try:
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            hbm_peak, hbm_src = float(mp["hbm_gbs"]), "MEASURED_PEAKS.json"
+        except Exception:  # noqa: BLE001
+            hbm_peak, hbm_src = 6650.0, "fallback"
+        T = D * (D + 1) // 2
+        L = r["state"]["nr"]
+        pre_bytes = P * (4 * (D + T) + 8) + 12 * L + 24 * L + N * (4 * D + 12) + 24 * N
+        line = {
+            "metric": METRIC, "value": N * world * K / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": max(3, args.warmup), "ms_per_step": tot_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {D}D, P={P} Gaussians x {N} query points per GPU "
+                                   f"({'x'.join([str(WORKLOADS[args.workload][2])] * D)} grid slab), C={C}, "
+                                   f"fn={['gaussian', 'derivative', 'laplacian', 'third'][fn]}, "
+                                   "step = preprocess(binning)+forward+backward"
+                                   + ("+1 NCCL allreduce of the grads" if world > 1 else ""),
+                       "l2": "160 MB buffer written between timed steps; inputs (134 MB samples) exceed L2",
+                       "tau": float(dgs.plan_of(r["state"]["gb"], r["state"]["nr"]).tau)},
+            "breakdown_ms": {"preprocess": pre_ms, "forward": fwd_ms, "backward": bwd_ms},
+            "fwd_bwd_only_points_per_s": N / ((fwd_ms + bwd_ms) * 1e-3),
+            "pairs_evaluated_per_pass": pairs, "pairs_per_point": pairs / N,
+            "gpu_launches": int(r["launches"]),
+            "clocks": r["clocks"],
+            "roofline": {"kernel": "dgs_backward_kernel", "bound": "fp32", "achieved": ach_bwd, "peak": peaks["fp32_tflops"],
+                         "unit": "TFLOP/s", "frac": ach_bwd / peaks["fp32_tflops"], "traffic": None,
+                         "peak_source": "FFMA microbenchmark (dgs_microbench) measured in this run, burst",
+                         "flop_per_pair": f_bwd, "launch_ms": bwd_ms,
+                         "sfu_frac": pairs / (bwd_ms * 1e-3) / 1e12 / peaks["ex2_tera_per_s"],
+                         "forward": {"kernel": "dgs_forward_kernel", "achieved": ach_fwd, "frac": ach_fwd / peaks["fp32_tflops"],
+                                     "flop_per_pair": f_fwd, "launch_ms": fwd_ms,
+                                     "sfu_frac": pairs / (fwd_ms * 1e-3) / 1e12 / peaks["ex2_tera_per_s"]},
+                         "binning": {"bound": "hbm", "achieved": pre_bytes / (pre_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                                     "unit": "GB/s", "frac": pre_bytes / (pre_ms * 1e-3) / 1e9 / hbm_peak,
+                                     "peak_source": hbm_src, "algorithmic_bytes": pre_bytes, "ms": pre_ms}},
+        }
+        if r["e2e"]:
+            line["e2e"] = {"value": N * world * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": r["e2e"]["h2d"],
+                           "d2h_bytes_per_step": r["e2e"]["d2h"], "ms_per_step": e2e_ms / K}
+        if not args.no_cpu_baseline and world >= 1:
+            try:
+                line["cpu_baseline"] = cpu_port_baseline(args.workload, 16 if P >= 1_000_000 else 32)
+            except Exception as ex:  # noqa: BLE001
+                line["cpu_baseline"] = {"error": repr(ex)[:200]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -48,6 +48,7 @@ EXPORTS = {
     "dgs_abi_version": (ctypes.c_int, []),
     "dgs_plan_sizeof": (c_sz, []),
     "dgs_last_error": (ctypes.c_char_p, []),
+    "dgs_launch_count": (ctypes.c_ulonglong, []),
     "dgs_geom_bytes": (c_sz, [c_i64, c_i64, ctypes.c_int]),
     "dgs_public_bytes": (c_sz, [c_u64]),
     "dgs_plan_begin": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_i64, ctypes.c_int, c_vp, c_f32, c_vp, c_sz,
@@ -59,6 +60,7 @@ EXPORTS = {
                                           c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_sample_backward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
                                            c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dgs_microbench": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, ctypes.POINTER(ctypes.c_double), c_vp]),
     "dgs_count_pairs": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp]),
 }
 

@@ -9,6 +9,7 @@
 #include "dgs_preprocess.cuh"
 
 static thread_local char g_err[512] = "";
+unsigned long long g_dgs_launches = 0;
 void dgs_set_error(const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -432,3 +433,5 @@ extern "C" __attribute__((visibility("default"))) int dgs_count_pairs(const dgs_
 }
 
 extern "C" __attribute__((visibility("default"))) size_t dgs_plan_sizeof(void) { return sizeof(dgs_plan_t); }
+
+extern "C" __attribute__((visibility("default"))) unsigned long long dgs_launch_count(void) { return g_dgs_launches; }

@@ -292,6 +292,7 @@ float dgs_tau_for(const dgs_plan_t* plan, int fn);
 template <int D, int FN, int CB>
 static int bwd_launch_cb(const BwdArgs& a, int n_coarse, bool exact, cudaStream_t st) {
     constexpr size_t smem = BwdLayout<D, FN, CB>::SMEM;
+    DGS_NOTE_LAUNCHES(1);
     if (exact) {
         auto k = dgs_backward_kernel<D, FN, CB, true>;
         DGS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

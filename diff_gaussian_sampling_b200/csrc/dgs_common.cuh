@@ -14,6 +14,10 @@
 #define DGS_TAU_STEP 2.0f
 #define DGS_TAU_MAX_EXTRA 6.0f   // tile lists are built for tau + 3*step
 
+// --- launch accounting (bench.py reports gpu_launches) -------------------------------
+extern unsigned long long g_dgs_launches;
+#define DGS_NOTE_LAUNCHES(n) (g_dgs_launches += (unsigned long long)(n))
+
 // --- error plumbing ------------------------------------------------------------------
 void dgs_set_error(const char* fmt, ...);
 #define DGS_CUDA(call)                                                                   \

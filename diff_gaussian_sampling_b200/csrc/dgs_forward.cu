@@ -154,6 +154,7 @@ float dgs_tau_for(const dgs_plan_t* plan, int fn) { return plan->tau + DGS_TAU_S
 
 template <int D, int FN, int CB>
 static void fwd_launch_cb(const FwdArgs& a, int n_coarse, bool exact, cudaStream_t st) {
+    DGS_NOTE_LAUNCHES(1);
     if (exact) dgs_forward_kernel<D, FN, CB, true, false><<<n_coarse, DGS_THREADS, 0, st>>>(a);
     else dgs_forward_kernel<D, FN, CB, false, false><<<n_coarse, DGS_THREADS, 0, st>>>(a);
 }

@@ -67,11 +67,14 @@ int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, c
     else if (D == 2) dgs_bounds_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
     else dgs_bounds_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
     dgs_bounds_finalize_kernel<<<1, 32, 0, st>>>(h, D);
+    DGS_NOTE_LAUNCHES(1);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
 int dgs_launch_header_init(DgsDevHeader* h, cudaStream_t st) {
     dgs_header_init_kernel<<<1, 32, 0, st>>>(h);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -142,8 +145,11 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
         for (int d = 0; d < D; d++) {
             const float m = means[i * D + d];
             r.mu[d] = m;
-            const float reach = fmaxf(fabsf(m - h->lo[d]), fabsf(m - h->hi[d]));
-            if (!(reach < 1.999f)) far = true;   // |mean - sample| may reach 2: fmod wrap quirk
+            // fp32 subtraction is monotone, so |fl(m - x)| <= max(|fl(m - lo)|, |fl(m - hi)|) for every
+            // sample x in [lo, hi]: exactly the pairs for which the fmod arm of forward.cu:150-156
+            // differs from X -/+ 2
+            const float reach = fmaxf(fabsf(__fsub_rn(m, h->lo[d])), fabsf(__fsub_rn(m, h->hi[d])));
+            if (!(reach < 2.0f)) far = true;
         }
         if (far) hflags |= DGS_HDR_EXACT_WRAP;
         if (!finite || far) {
@@ -191,6 +197,7 @@ int dgs_launch_crec(const float* means, const float* conics, int64_t P, int D, f
     if (D == 1) dgs_crec_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
     else if (D == 2) dgs_crec_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
     else dgs_crec_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -243,6 +250,7 @@ int dgs_launch_gauss_preprocess(const float* means, const float* cov, int64_t P,
     if (D == 1) dgs_gauss_preprocess_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, cov, P, G, radii, touched);
     else if (D == 2) dgs_gauss_preprocess_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, cov, P, G, radii, touched);
     else dgs_gauss_preprocess_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, cov, P, G, radii, touched);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -300,6 +308,7 @@ int dgs_launch_duplicate(const float* means, const float* radii, const uint32_t*
     if (D == 1) dgs_duplicate_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, radii, offsets, P, G, keys, vals);
     else if (D == 2) dgs_duplicate_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, radii, offsets, P, G, keys, vals);
     else dgs_duplicate_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, radii, offsets, P, G, keys, vals);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -326,6 +335,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_ranges_kernel(const uint64_t*
 int dgs_launch_ranges(const uint64_t* keys, int64_t L, void* ranges, int n_ranges, cudaStream_t st) {
     if (L <= 0) return 0;
     dgs_ranges_kernel<<<dgs_cdiv(L, DGS_THREADS), DGS_THREADS, 0, st>>>(keys, L, (uint2*)ranges, n_ranges);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -480,6 +490,7 @@ int dgs_launch_sample_keys(const float* samples, const dgs_plan_t* plan, uint64_
     if (plan->D == 1) dgs_sample_keys_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
     else if (plan->D == 2) dgs_sample_keys_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
     else dgs_sample_keys_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -492,6 +503,7 @@ int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const 
     if (plan->D == 1) dgs_fine_scatter_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, N, tile_of, rank_of, fine_start, fine_ids, fine_xyz);
     else if (plan->D == 2) dgs_fine_scatter_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, N, tile_of, rank_of, fine_start, fine_ids, fine_xyz);
     else dgs_fine_scatter_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, N, tile_of, rank_of, fine_start, fine_ids, fine_xyz);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -503,6 +515,7 @@ int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const ui
     if (plan->D == 1) dgs_tile_aabb_kernel<1><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
     else if (plan->D == 2) dgs_tile_aabb_kernel<2><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
     else dgs_tile_aabb_kernel<3><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -561,6 +574,7 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const DgsCu
     else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, coarse_aabb, n1, n1_off, keys, vals);
     if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
 #undef L1_LAUNCH
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -583,6 +597,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_start_kernel(const uint32_
 int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uint32_t* start, cudaStream_t st) {
     const int64_t work = n == 0 ? (int64_t)n_tiles + 1 : n + 1;
     dgs_l1_start_kernel<<<dgs_cdiv(work, DGS_THREADS), DGS_THREADS, 0, st>>>(keys_sorted, n, n_tiles, start);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }

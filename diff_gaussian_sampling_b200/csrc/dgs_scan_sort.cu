@@ -120,6 +120,7 @@ static int scan_impl(const uint32_t* in, uint32_t* out, int64_t n, void* tmp, ui
     scan_reduce_kernel<<<nb, DGS_THREADS, 0, st>>>(in, n, bs);
     scan_spine_kernel<<<1, DGS_THREADS, 0, st>>>(bs, nb, total_out);
     scan_apply_kernel<INCLUSIVE><<<nb, DGS_THREADS, 0, st>>>(in, out, n, bs);
+    DGS_NOTE_LAUNCHES(3);
     DGS_LAUNCH_CHECK();
     return 0;
 }
@@ -244,6 +245,7 @@ static int sort_impl(const K* keys_in, const uint32_t* vals_in, K* keys_out, uin
     const int passes = bits <= 0 ? 0 : (bits + 7) / 8;
     if (passes == 0) {
         pair_copy_kernel<K><<<dgs_cdiv(n, DGS_THREADS), DGS_THREADS, 0, st>>>(keys_in, vals_in, keys_out, vals_out, n);
+        DGS_NOTE_LAUNCHES(1);
         DGS_LAUNCH_CHECK();
         return 0;
     }
@@ -265,6 +267,7 @@ static int sort_impl(const K* keys_in, const uint32_t* vals_in, K* keys_out, uin
         if (rc) return rc;
         radix_scatter_kernel<K><<<n_chunks, DGS_THREADS, 0, st>>>(src_k, src_v, dst_k, dst_v, n, shift, mask, nd, n_chunks, hist);
         DGS_LAUNCH_CHECK();
+        DGS_NOTE_LAUNCHES(2);
         src_k = dst_k;
         src_v = dst_v;
     }

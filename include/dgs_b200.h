@@ -96,6 +96,8 @@ typedef struct dgs_plan {
 int         dgs_abi_version(void);
 size_t      dgs_plan_sizeof(void);   /* sizeof(dgs_plan_t) the library was built with */
 const char* dgs_last_error(void);
+/* number of CUDA kernels this library has launched in this process so far */
+unsigned long long dgs_launch_count(void);
 
 /* Bytes of the preprocess scratch ("geometry buffer"; reference GeometryState,
  * sampler_impl.cu:191-198 — radii live outside it here, as a caller tensor). */
@@ -183,6 +185,10 @@ int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C,
  * zero-filled uint64 on the device.  Asynchronous. */
 int dgs_count_pairs(const dgs_plan_t* plan, int fn, const void* binning_dev, const void* sample_binning_dev,
                     unsigned long long* counter_dev, void* stream);
+
+/* Roofline denominators measured live (bench.py): which 0 = FP32 FFMA, 1 = MUFU.EX2.  Launches one
+ * kernel on `stream`; *work_out = flop (FFMA counted as 2) resp. ex2 operations of that launch. */
+int dgs_microbench(int which, int iters, float* out_dev, double* work_out, void* stream);
 
 #ifdef __cplusplus
 }
