@@ -32,7 +32,7 @@ class Plan(ctypes.Structure):
         ("g_sort_tmp_off", c_u64),
         ("s_plan_off", c_u64), ("s_fine_start_off", c_u64), ("s_fine_ids_off", c_u64), ("s_fine_xyz_off", c_u64),
         ("s_fine_aabb_off", c_u64), ("s_coarse_aabb_off", c_u64), ("s_tmp_off", c_u64),
-        ("reserved", c_i32 * 8),
+        ("g_prec_off", c_u64), ("reserved", c_i32 * 6),
     ]
 
     def as_dict(self):

@@ -144,6 +144,7 @@ static void gauss_layout(dgs_plan_t* pl) {
     pl->g_crec_off = o; o = dgs_a128(o + p * sizeof(DgsCullRec));
     pl->g_l1_start_off = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     pl->g_l1_ids_off = o; o = dgs_a128(o + (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * 4);
+    pl->g_prec_off = o; o = dgs_a128(o + p * (size_t)(pl->D == 3 ? 12 : 8) * 4);
     pl->g_sort_tmp_off = o; o += gauss_tmp_layout(pl).total;
     pl->binning_bytes = o + 128;
 }
@@ -399,27 +400,27 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_from_buffer(const
 // forward / backward
 // ---------------------------------------------------------------------------------------
 extern "C" __attribute__((visibility("default"))) int dgs_sample_forward(const dgs_plan_t* plan, int fn, int C, const float* means_dev, const float* values_dev,
-                                  const float* conics_dev, const float* samples_dev, const void* binning_dev,
+                                  const float* conics_dev, const float* samples_dev, void* binning_dev,
                                   const void* sample_binning_dev, const void* ranges_dev, const void* sample_ranges_dev,
                                   float* out_dev, void* stream) {
     (void)samples_dev; (void)sample_ranges_dev;
     int rc = check_plan(plan);
     if (rc) return rc;
     DGS_REQUIRE(fn >= 0 && fn <= 3 && C >= 1, DGS_ERR_BAD_ARG, "fn must be 0..3 and C >= 1");
-    return dgs_launch_forward(plan, fn, C, means_dev, values_dev, conics_dev, (const uint8_t*)binning_dev,
+    return dgs_launch_forward(plan, fn, C, means_dev, values_dev, conics_dev, (uint8_t*)binning_dev,
                               (const uint8_t*)sample_binning_dev, ranges_dev, out_dev, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" __attribute__((visibility("default"))) int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C, const float* means_dev, const float* values_dev,
                                    const float* conics_dev, const float* samples_dev, const float* dout_dev,
-                                   const void* binning_dev, const void* sample_binning_dev, const void* ranges_dev,
+                                   void* binning_dev, const void* sample_binning_dev, const void* ranges_dev,
                                    const void* sample_ranges_dev, float* dmeans_dev, float* dvalues_dev, float* dconics_dev,
                                    void* stream) {
     (void)samples_dev; (void)sample_ranges_dev;
     int rc = check_plan(plan);
     if (rc) return rc;
     DGS_REQUIRE(fn >= 0 && fn <= 3 && C >= 1, DGS_ERR_BAD_ARG, "fn must be 0..3 and C >= 1");
-    return dgs_launch_backward(plan, fn, C, means_dev, values_dev, conics_dev, dout_dev, (const uint8_t*)binning_dev,
+    return dgs_launch_backward(plan, fn, C, means_dev, values_dev, conics_dev, dout_dev, (uint8_t*)binning_dev,
                                (const uint8_t*)sample_binning_dev, ranges_dev, dmeans_dev, dvalues_dev, dconics_dev,
                                (cudaStream_t)stream);
 }
@@ -428,7 +429,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_count_pairs(const dgs_
                                unsigned long long* counter_dev, void* stream) {
     int rc = check_plan(plan);
     if (rc) return rc;
-    return dgs_launch_forward(plan, fn, 1, nullptr, nullptr, nullptr, (const uint8_t*)binning_dev,
+    return dgs_launch_forward(plan, fn, 1, nullptr, nullptr, nullptr, (uint8_t*)const_cast<void*>(binning_dev),
                               (const uint8_t*)sample_binning_dev, nullptr, nullptr, counter_dev, (cudaStream_t)stream);
 }
 

@@ -3,25 +3,34 @@
 //
 // The reference issues D + C + D(D+1)/2 global float atomics PER PAIR, with all 256 threads of a
 // CTA hitting the same Gaussian row at once (backward.cu:100, e.g. :140-152).  Here the loop is
-// transposed: after the same per-fine-tile culling as the forward, a thread owns one
-// (Gaussian, sample-group) item — 8 groups per batch of <= 256 samples, 8 adjacent lanes per
-// Gaussian — and accumulates the gradient of ITS Gaussian over ITS group's samples in
-// registers, reading the samples (x, symmetrised dL/dout) from shared memory.  Three
-// shuffle-xor steps combine the 8 groups and one lane issues the D + C + T atomics per
-// (Gaussian, batch): >= 256x fewer global atomics, none of them same-address within a warp.
-//
-// Gradient formulas: general-D analytic VJP of  sum_u W_u H_u(a, C) * G  (dgs_field.cuh);
-// identical to the reference's hand-expanded D<=2 bodies (checked against golden vectors),
-// except D==1 `third` dL/dconic where the reference's expression (backward.cu:304-328)
-// differs from the analytic one — reproduced literally for drop-in parity.
+// transposed and every warp works alone on one fine tile (no CTA barrier):
+//   1. the warp stages the tile's samples (coordinates + symmetrised dL/dout) in its private
+//      shared-memory slice;
+//   2. it streams the coarse tile's Gaussian list, culls against the box of the tile's samples
+//      (same test as the forward) and queues the surviving ids;
+//   3. whenever 32*G ids are queued, every LANE takes G Gaussians into registers and walks all
+//      samples of the tile (uniform shared-memory broadcast reads, amortised over the lane's G
+//      Gaussians), accumulating in registers — no shuffles, no atomics in the loop;
+//   4. one set of global reductions per (Gaussian, fine tile).
+// `gaussian` (fn 0) accumulates the weighted moments  sum w, sum w X, sum w X X^T  of the
+// displacement (w = G dL/dout v) and a finalize kernel turns them into dL/dmeans = -C m1 and
+// dL/dconics = -(1/2 | 1) m2: 2 FADD + 5 FMUL/FFMA + MUFU.EX2 + 9 FMUL/FADD/FFMA per pair in 2D.
+// Higher orders use the general-D analytic VJP of sum_u W_u H_u(a, C) G (dgs_field.cuh), identical
+// to the reference's hand-expanded D<=2 bodies (checked against golden vectors) except D==1
+// `third` dL/dconic, where the reference's expression (backward.cu:304-328) differs from the
+// analytic one — reproduced literally for drop-in parity.
 #include "dgs_field.cuh"
 #include "dgs_math.cuh"
 
-#define BWD_CAP 512
-#define BWD_GROUPS 8
+#define BWD_WARPS 4
+#define BWD_THREADS (BWD_WARPS * 32)
+#define BWD_QF 96    // fast-id queue slots per warp
+#define BWD_QG 64    // general-id queue slots per warp
+#define BWD_EXACT_BIT 0x80000000u
 
 struct BwdArgs {
-    const float* means; const float* values; const float* conics; const float* dout;
+    const float* values; const float* conics; const float* dout;
+    const float* prec;
     const DgsCullRec* crec;
     const uint32_t* l1_start; const uint32_t* l1_ids;
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
@@ -33,33 +42,242 @@ struct BwdArgs {
 };
 
 template <int D, int FN, int CB>
-struct BwdLayout {
+struct BwdCfg {
     static constexpr int T = D * (D + 1) / 2;
     static constexpr int U = dgs_nuniq(D, FN);
-    static constexpr int GW = (1 + D + T + CB + 3) / 4 * 4;        // Gaussian record (id first)
-    static constexpr int SW0 = (D + U * CB + 3) / 4 * 4;           // sample record
-    static constexpr int SW = ((SW0 / 4) & 1) ? SW0 : SW0 + 4;     // odd number of 16-B units: conflict-free
-    static constexpr int SLOTS = BWD_GROUPS * 33;
-    static constexpr size_t SMEM = (size_t)(BWD_CAP * GW + SLOTS * SW) * 4;
+    static constexpr int AFULL = dgs_ipow(D, FN);
+    static constexpr int SW0 = D + U * CB;                  // x | dOs[u][c]
+    static constexpr int SW = (SW0 + 3) / 4 * 4;
+    static constexpr int SAMP_FLOATS = 256 * SW < 2048 ? 256 * SW : 2048;
+    static constexpr int SCAP = SAMP_FLOATS / SW;           // samples per pass
+    static constexpr int G = FN == 0 ? 2 : 1;               // Gaussians per lane on the fast path
+    static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG;
 };
 
-template <int D, int FN, int CB, bool EXACT>
-__global__ void __launch_bounds__(DGS_THREADS) dgs_backward_kernel(const BwdArgs A) {
-    using L = BwdLayout<D, FN, CB>;
-    constexpr int T = L::T, U = L::U, GW = L::GW, SW = L::SW;
-    constexpr int AFULL = dgs_ipow(D, FN);
-    extern __shared__ __align__(16) float smem[];
-    float* stage = smem;                 // BWD_CAP * GW
-    float* samp = smem + BWD_CAP * GW;   // SLOTS * SW
-    __shared__ uint32_t s_wc[DGS_THREADS / 32];
+// per-pair VJP for FN >= 1: accumulates dV[c], dM[m], dC[k] (already multiplied by G)
+template <int D, int FN, int CB>
+__device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G, const float* con, const float* val,
+                                         const float* dOs, float* dV, float* dM, float* dC) {
+    constexpr int T = D * (D + 1) / 2;
+    constexpr int U = dgs_nuniq(D, FN);
+    float H[U];
+    dgs_hermite<D, FN>(a, con, H);
+    // hd_c = sum_u H_u dOs[u][c];  W_u = sum_c v_c dOs[u][c];  S = sum_c v_c hd_c
+    float S = 0.f;
+    float Wu[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) Wu[u] = 0.f;
+#pragma unroll
+    for (int c = 0; c < CB; c++) {
+        float hd = 0.f;
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const float d_ = dOs[u * CB + c];
+            hd = fmaf(H[u], d_, hd);
+            Wu[u] = fmaf(val[c], d_, Wu[u]);
+        }
+        dV[c] = fmaf(G, hd, dV[c]);
+        S = fmaf(val[c], hd, S);
+    }
+    float dSda[D], dSdC[T];
+#pragma unroll
+    for (int d = 0; d < D; d++) dSda[d] = 0.f;
+#pragma unroll
+    for (int k = 0; k < T; k++) dSdC[k] = 0.f;
+    if (FN == 1) {
+#pragma unroll
+        for (int i = 0; i < D; i++) dSda[i] = Wu[i];
+    } else if (FN == 2) {
+#pragma unroll
+        for (int i = 0; i < D; i++)
+#pragma unroll
+            for (int jx = i; jx < D; jx++) {
+                const float Wv = Wu[dgs_tri(D, i, jx)];
+                dSda[i] = fmaf(Wv, a[jx], dSda[i]);
+                dSda[jx] = fmaf(Wv, a[i], dSda[jx]);
+                dSdC[dgs_tri(D, i, jx)] -= Wv;
+            }
+    } else if (FN == 3) {
+        int u = 0;
+#pragma unroll
+        for (int i = 0; i < D; i++)
+#pragma unroll
+            for (int jx = i; jx < D; jx++)
+#pragma unroll
+                for (int k = jx; k < D; k++) {
+                    const float Wv = Wu[u++];
+                    const float cij = con[dgs_tri(D, i, jx)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, jx, k)];
+                    dSda[k] = fmaf(Wv, fmaf(-a[i], a[jx], cij), dSda[k]);
+                    dSda[jx] = fmaf(Wv, fmaf(-a[i], a[k], cik), dSda[jx]);
+                    dSda[i] = fmaf(Wv, fmaf(-a[jx], a[k], cjk), dSda[i]);
+                    dSdC[dgs_tri(D, i, jx)] = fmaf(Wv, a[k], dSdC[dgs_tri(D, i, jx)]);
+                    dSdC[dgs_tri(D, i, k)] = fmaf(Wv, a[jx], dSdC[dgs_tri(D, i, k)]);
+                    dSdC[dgs_tri(D, jx, k)] = fmaf(Wv, a[i], dSdC[dgs_tri(D, jx, k)]);
+                }
+    }
+#pragma unroll
+    for (int m = 0; m < D; m++) {
+        float g = -a[m] * S;
+#pragma unroll
+        for (int i = 0; i < D; i++) g = fmaf(dSda[i], con[dgs_tri_sym(D, i, m)], g);
+        dM[m] = fmaf(G, g, dM[m]);
+    }
+    if (D == 1 && FN == 3) {
+        // backward.cu:304-328, literally (differs from the analytic VJP)
+        const float X0 = X[0], x1 = a[0], c0 = con[0];
+        const float g = 2.f * X0 * X0 - 2.f * x1 * x1 * X0 - 0.5f * (2.f * X0 * x1 - X0) * X0 * X0
+                        + 0.5f * (x1 * x1 - c0) * x1 * X0 * X0;
+        dC[0] = fmaf(G, g * Wu[0], dC[0]);
+    } else {
+#pragma unroll
+        for (int m = 0; m < D; m++)
+#pragma unroll
+            for (int n = m; n < D; n++) {
+                const float kf = (m == n) ? -0.5f : -1.0f;
+                float g = kf * X[m] * X[n] * S;
+                g = fmaf(dSda[m], X[n], g);
+                if (m != n) g = fmaf(dSda[n], X[m], g);
+                g += dSdC[dgs_tri(D, m, n)];
+                dC[dgs_tri(D, m, n)] = fmaf(G, g, dC[dgs_tri(D, m, n)]);
+            }
+    }
+}
 
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+// One batch: every lane owns NG Gaussians (queue entries lane, lane+32, ...) and walks the np
+// staged samples.  FAST: whitened geometry without wrap; otherwise the literal reference pair.
+template <int D, int FN, int CB, int NG, bool FAST, bool VPOST>
+__device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restrict__ sS, int np,
+                                          const uint32_t* __restrict__ queue, int count, int lane) {
+    using K = BwdCfg<D, FN, CB>;
+    constexpr int T = K::T, U = K::U, SW = K::SW, SW0 = K::SW0;
+    constexpr int PW = DGS_PREC_W(D);
+    uint32_t id[NG];
+    bool valid[NG], exact[NG];
+    float mu[NG][D], geo[NG][T], con[NG][T], val[NG][CB];
+    float dV[NG][CB], dM[NG][D], dC[NG][T];
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+        const int qi = lane + 32 * g;
+        valid[g] = qi < count;
+        const uint32_t ent = queue[valid[g] ? qi : 0];
+        id[g] = ent & ~BWD_EXACT_BIT;
+        exact[g] = (ent & BWD_EXACT_BIT) != 0u;
+        const float4* p4 = (const float4*)(A.prec + (int64_t)id[g] * PW);
+        float pr[PW];
+#pragma unroll
+        for (int q = 0; q < PW / 4; q++) {
+            const float4 v = __ldg(p4 + q);
+            pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
+        }
+#pragma unroll
+        for (int d = 0; d < D; d++) mu[g][d] = pr[d];
+#pragma unroll
+        for (int k = 0; k < T; k++) {
+            geo[g][k] = pr[D + k];
+            con[g][k] = (FN > 0 || !FAST) ? A.conics[(int64_t)id[g] * T + k] : 0.f;
+        }
+#pragma unroll
+        for (int c = 0; c < CB; c++) {
+            val[g][c] = A.values[(int64_t)id[g] * A.C + A.ch0 + c];
+            dV[g][c] = 0.f;
+        }
+#pragma unroll
+        for (int d = 0; d < D; d++) dM[g][d] = 0.f;
+#pragma unroll
+        for (int k = 0; k < T; k++) dC[g][k] = 0.f;
+    }
+    for (int s = 0; s < np; s++) {
+        float sr[SW];
+#pragma unroll
+        for (int q = 0; q < SW / 4; q++) {
+            if (q * 4 < SW0) {
+                const float4 v = *(const float4*)(sS + s * SW + q * 4);
+                sr[q * 4] = v.x; sr[q * 4 + 1] = v.y; sr[q * 4 + 2] = v.z; sr[q * 4 + 3] = v.w;
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            float X[D], a[D], Gv;
+            if (FAST) {
+#pragma unroll
+                for (int d = 0; d < D; d++) X[d] = mu[g][d] - sr[d];
+                Gv = dgs_white_G<D>(X, geo[g]);
+                if (FN > 0) dgs_conic_times<D>(con[g], X, a);
+            } else {
+                if (exact[g]) {
+                    DgsPair<D, FN, true, true> p;
+                    p.eval(sr, mu[g], con[g]);
+#pragma unroll
+                    for (int d = 0; d < D; d++) { X[d] = p.X[d]; a[d] = p.a[d]; }
+                    Gv = p.G;
+                } else {
+                    DgsPair<D, FN, false, true> p;
+                    p.eval(sr, mu[g], con[g]);
+#pragma unroll
+                    for (int d = 0; d < D; d++) { X[d] = p.X[d]; a[d] = p.a[d]; }
+                    Gv = p.G;
+                }
+            }
+            if (FN == 0) {
+                float w;
+                if (VPOST) {           // single channel: v is applied by the finalize kernel
+                    w = Gv * sr[D];
+                    dV[g][0] += w;
+                } else {
+                    float S = 0.f;
+#pragma unroll
+                    for (int c = 0; c < CB; c++) {
+                        dV[g][c] = fmaf(Gv, sr[D + c], dV[g][c]);
+                        S = fmaf(val[g][c], sr[D + c], S);
+                    }
+                    w = Gv * S;
+                }
+                float wX[D];
+#pragma unroll
+                for (int d = 0; d < D; d++) {
+                    wX[d] = w * X[d];
+                    dM[g][d] += wX[d];
+                }
+#pragma unroll
+                for (int i = 0; i < D; i++)
+#pragma unroll
+                    for (int j = i; j < D; j++) dC[g][dgs_tri(D, i, j)] = fmaf(wX[i], X[j], dC[g][dgs_tri(D, i, j)]);
+            } else {
+                bwd_pair<D, FN, CB>(X, a, Gv, con[g], val[g], sr + D, dV[g], dM[g], dC[g]);
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+        if (valid[g]) {
+#pragma unroll
+            for (int c = 0; c < CB; c++) atomicAdd(A.dvalues + (int64_t)id[g] * A.C + A.ch0 + c, dV[g][c]);
+#pragma unroll
+            for (int d = 0; d < D; d++) atomicAdd(A.dmeans + (int64_t)id[g] * D + d, dM[g][d]);
+#pragma unroll
+            for (int k = 0; k < T; k++) atomicAdd(A.dconics + (int64_t)id[g] * T + k, dC[g][k]);
+        }
+    }
+}
+
+template <int D, int FN, int CB, bool VPOST>
+__global__ void __launch_bounds__(BWD_THREADS) dgs_backward_kernel(const BwdArgs A) {
+    using K = BwdCfg<D, FN, CB>;
+    constexpr int U = K::U, AFULL = K::AFULL, SW = K::SW, SW0 = K::SW0, SCAP = K::SCAP, NG = K::G;
+    constexpr int PW = DGS_PREC_W(D);
+    __shared__ __align__(16) float smem[BWD_WARPS * K::WARP_WORDS];
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    float* sS = smem + warp * K::WARP_WORDS;
+    uint32_t* qF = (uint32_t*)(sS + K::SAMP_FLOATS);
+    uint32_t* qG = qF + BWD_QF;
     const int64_t coarse = blockIdx.x;
     if (__float_as_int(A.coarse_aabb[coarse * 8 + 6]) == 0) return;
     const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
     if (g0 == g1) return;
 
-    for (int ft = 0; ft < A.fpcD; ft++) {
+    for (int ft = warp; ft < A.fpcD; ft += BWD_WARPS) {
         const int64_t tile = coarse * A.fpcD + ft;
         const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
         if (s0 == s1) continue;
@@ -69,274 +287,166 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_backward_kernel(const BwdArgs
             const float4 b1 = *(const float4*)(A.fine_aabb + tile * 8 + 4);
             lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b0.w; hi[1] = b1.x; hi[2] = b1.y;
         }
-        for (uint32_t sb = s0; sb < s1; sb += DGS_THREADS) {
-            const int nb = (int)min((uint32_t)DGS_THREADS, s1 - sb);
-            const int gs = (nb + BWD_GROUPS - 1) / BWD_GROUPS;
-            const int stride = gs | 1;
-            // ---- stage the samples of this batch: x and the symmetrised dL/dout ----
-            for (int slot = tid; slot < BWD_GROUPS * stride; slot += DGS_THREADS) {
-                const int g = slot / stride, j = slot - g * stride;
-                const int sl = g * gs + j;
-                float* r = samp + (size_t)slot * SW;
-                if (j < gs && sl < nb) {
-                    const uint32_t jj = sb + sl;
-                    const uint32_t sid = A.fine_ids[jj];
+        const uint32_t n = s1 - s0;
+        const uint32_t n_pass = (n + SCAP - 1) / SCAP;
+        const uint32_t per = (n + n_pass - 1) / n_pass;
+        for (uint32_t pb = s0; pb < s1; pb += per) {
+            const int np = (int)(min(s1, pb + per) - pb);
+            __syncwarp();
+            // ---- stage the samples of this pass: x and the symmetrised dL/dout ----
+            for (int sl = lane; sl < np; sl += 32) {
+                const uint32_t jj = pb + sl;
+                const uint32_t sid = A.fine_ids[jj];
+                float* r = sS + sl * SW;
 #pragma unroll
-                    for (int d = 0; d < D; d++) r[d] = A.fine_xyz[(int64_t)d * A.N + jj];
-                    float ds[U][CB];
+                for (int d = 0; d < D; d++) r[d] = A.fine_xyz[(int64_t)d * A.N + jj];
+                float ds[U][CB];
 #pragma unroll
-                    for (int u = 0; u < U; u++)
+                for (int u = 0; u < U; u++)
 #pragma unroll
-                        for (int c = 0; c < CB; c++) ds[u][c] = 0.f;
-                    const float* dp = A.dout + (int64_t)sid * AFULL * A.C + A.ch0;
+                    for (int c = 0; c < CB; c++) ds[u][c] = 0.f;
+                const float* dp = A.dout + (int64_t)sid * AFULL * A.C + A.ch0;
 #pragma unroll
-                    for (int al = 0; al < AFULL; al++)
+                for (int al = 0; al < AFULL; al++)
 #pragma unroll
-                        for (int c = 0; c < CB; c++) ds[dgs_uniq_of(D, FN, al)][c] += dp[(int64_t)al * A.C + c];
+                    for (int c = 0; c < CB; c++) ds[dgs_uniq_of(D, FN, al)][c] += dp[(int64_t)al * A.C + c];
 #pragma unroll
-                    for (int u = 0; u < U; u++)
+                for (int u = 0; u < U; u++)
 #pragma unroll
-                        for (int c = 0; c < CB; c++) r[D + u * CB + c] = ds[u][c];
-                } else {
-#pragma unroll
-                    for (int q = 0; q < D + U * CB; q++) r[q] = 0.f;
-                }
+                    for (int c = 0; c < CB; c++) r[D + u * CB + c] = ds[u][c];
             }
-            __syncthreads();
+            __syncwarp();
 
-            uint32_t staged = 0;
-            for (uint32_t base = g0; base < g1; base += DGS_THREADS) {
-                const uint32_t e = base + tid;
-                bool pass = false;
+            int nf = 0, ng = 0;
+            for (uint32_t base = g0; base < g1; base += 32) {
+                const uint32_t e = base + lane;
+                bool pass = false, fast = false, exact = false;
                 uint32_t id = 0;
                 if (e < g1) {
                     id = A.l1_ids[e];
                     const DgsCullRec rec = A.crec[id];
                     pass = dgs_cull_pass<D>(rec, lo, hi, A.shrink, A.shrink2);
                 }
-                const uint32_t bal = __ballot_sync(0xffffffffu, pass);
-                if (lane == 0) s_wc[w] = __popc(bal);
-                __syncthreads();
-                uint32_t pre = 0, tot = 0;
-#pragma unroll
-                for (int k = 0; k < DGS_THREADS / 32; k++) {
-                    const uint32_t c = s_wc[k];
-                    pre += (k < w) ? c : 0u;
-                    tot += c;
-                }
                 if (pass) {
-                    float* r = stage + (size_t)(staged + pre + __popc(bal & ((1u << lane) - 1u))) * GW;
-                    r[0] = __uint_as_float(id);
+                    const float* pr = A.prec + (int64_t)id * PW;
+                    fast = (__float_as_uint(__ldg(pr + PW - 1)) & DGS_PREC_FAST) != 0u;
 #pragma unroll
-                    for (int d = 0; d < D; d++) r[1 + d] = A.means[(int64_t)id * D + d];
-#pragma unroll
-                    for (int k = 0; k < T; k++) r[1 + D + k] = A.conics[(int64_t)id * T + k];
-#pragma unroll
-                    for (int c = 0; c < CB; c++) r[1 + D + T + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
-                }
-                staged += tot;
-                const bool last = base + DGS_THREADS >= g1;
-                if (staged > BWD_CAP - DGS_THREADS || last) {
-                    __syncthreads();
-                    const int grp = tid & (BWD_GROUPS - 1);
-                    for (uint32_t it0 = 0; it0 < staged * BWD_GROUPS; it0 += DGS_THREADS) {
-                        const uint32_t gi = (it0 + tid) / BWD_GROUPS;
-                        const bool valid = gi < staged;
-                        float dV[CB], dM[D], dC[T];
-#pragma unroll
-                        for (int c = 0; c < CB; c++) dV[c] = 0.f;
-#pragma unroll
-                        for (int d = 0; d < D; d++) dM[d] = 0.f;
-#pragma unroll
-                        for (int k = 0; k < T; k++) dC[k] = 0.f;
-                        uint32_t gid = 0;
-                        if (valid) {
-                            float gr[GW];
-#pragma unroll
-                            for (int q = 0; q < GW / 4; q++) {
-                                const float4 v = *(const float4*)(stage + (size_t)gi * GW + q * 4);
-                                gr[q * 4 + 0] = v.x; gr[q * 4 + 1] = v.y; gr[q * 4 + 2] = v.z; gr[q * 4 + 3] = v.w;
-                            }
-                            gid = __float_as_uint(gr[0]);
-                            const float* mu = gr + 1;
-                            const float* con = gr + 1 + D;
-                            const float* val = gr + 1 + D + T;
-                            const float* sp = samp + (size_t)grp * stride * SW;
-                            for (int j = 0; j < gs; j++, sp += SW) {
-                                float sr[SW];
-#pragma unroll
-                                for (int q = 0; q < SW / 4; q++) {
-                                    if (q * 4 < D + U * CB) {
-                                        const float4 v = *(const float4*)(sp + q * 4);
-                                        sr[q * 4 + 0] = v.x; sr[q * 4 + 1] = v.y; sr[q * 4 + 2] = v.z; sr[q * 4 + 3] = v.w;
-                                    }
-                                }
-                                DgsPair<D, FN, EXACT, true> p;
-                                p.eval(sr, mu, con);
-                                float H[U];
-                                p.hermite(con, H);
-                                // hd_c = sum_u H_u dOs[u][c];  W_u = sum_c v_c dOs[u][c];  S = sum_c v_c hd_c
-                                float S = 0.f;
-                                float Wu[U];
-#pragma unroll
-                                for (int u = 0; u < U; u++) Wu[u] = 0.f;
-#pragma unroll
-                                for (int c = 0; c < CB; c++) {
-                                    float hd = 0.f;
-#pragma unroll
-                                    for (int u = 0; u < U; u++) {
-                                        const float d_ = sr[D + u * CB + c];
-                                        hd = fmaf(H[u], d_, hd);
-                                        Wu[u] = fmaf(val[c], d_, Wu[u]);
-                                    }
-                                    dV[c] = fmaf(p.G, hd, dV[c]);
-                                    S = fmaf(val[c], hd, S);
-                                }
-                                float dSda[D], dSdC[T];
-#pragma unroll
-                                for (int d = 0; d < D; d++) dSda[d] = 0.f;
-#pragma unroll
-                                for (int k = 0; k < T; k++) dSdC[k] = 0.f;
-                                if (FN == 1) {
-#pragma unroll
-                                    for (int i = 0; i < D; i++) dSda[i] = Wu[i];
-                                } else if (FN == 2) {
-#pragma unroll
-                                    for (int i = 0; i < D; i++)
-#pragma unroll
-                                        for (int jx = i; jx < D; jx++) {
-                                            const float Wv = Wu[dgs_tri(D, i, jx)];
-                                            dSda[i] = fmaf(Wv, p.a[jx], dSda[i]);
-                                            dSda[jx] = fmaf(Wv, p.a[i], dSda[jx]);
-                                            dSdC[dgs_tri(D, i, jx)] -= Wv;
-                                        }
-                                } else if (FN == 3) {
-                                    int u = 0;
-#pragma unroll
-                                    for (int i = 0; i < D; i++)
-#pragma unroll
-                                        for (int jx = i; jx < D; jx++)
-#pragma unroll
-                                            for (int k = jx; k < D; k++) {
-                                                const float Wv = Wu[u++];
-                                                const float cij = con[dgs_tri(D, i, jx)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, jx, k)];
-                                                dSda[k] = fmaf(Wv, fmaf(-p.a[i], p.a[jx], cij), dSda[k]);
-                                                dSda[jx] = fmaf(Wv, fmaf(-p.a[i], p.a[k], cik), dSda[jx]);
-                                                dSda[i] = fmaf(Wv, fmaf(-p.a[jx], p.a[k], cjk), dSda[i]);
-                                                dSdC[dgs_tri(D, i, jx)] = fmaf(Wv, p.a[k], dSdC[dgs_tri(D, i, jx)]);
-                                                dSdC[dgs_tri(D, i, k)] = fmaf(Wv, p.a[jx], dSdC[dgs_tri(D, i, k)]);
-                                                dSdC[dgs_tri(D, jx, k)] = fmaf(Wv, p.a[i], dSdC[dgs_tri(D, jx, k)]);
-                                            }
-                                }
-#pragma unroll
-                                for (int m = 0; m < D; m++) {
-                                    float g = -p.a[m] * S;
-                                    if (FN > 0) {
-#pragma unroll
-                                        for (int i = 0; i < D; i++) g = fmaf(dSda[i], con[dgs_tri_sym(D, i, m)], g);
-                                    }
-                                    dM[m] = fmaf(p.G, g, dM[m]);
-                                }
-                                if (D == 1 && FN == 3) {
-                                    // backward.cu:304-328, literally (differs from the analytic VJP)
-                                    const float X0 = p.X[0], x1 = p.a[0], c0 = con[0];
-                                    const float g = 2.f * X0 * X0 - 2.f * x1 * x1 * X0 - 0.5f * (2.f * X0 * x1 - X0) * X0 * X0
-                                                    + 0.5f * (x1 * x1 - c0) * x1 * X0 * X0;
-                                    dC[0] = fmaf(p.G, g * Wu[0], dC[0]);
-                                } else {
-#pragma unroll
-                                    for (int m = 0; m < D; m++)
-#pragma unroll
-                                        for (int n = m; n < D; n++) {
-                                            const float kf = (m == n) ? -0.5f : -1.0f;
-                                            float g = kf * p.X[m] * p.X[n] * S;
-                                            if (FN > 0) {
-                                                g = fmaf(dSda[m], p.X[n], g);
-                                                if (m != n) g = fmaf(dSda[n], p.X[m], g);
-                                                g += dSdC[dgs_tri(D, m, n)];
-                                            }
-                                            dC[dgs_tri(D, m, n)] = fmaf(p.G, g, dC[dgs_tri(D, m, n)]);
-                                        }
-                                }
-                            }
-                        }
-                        // combine the 8 sample groups of each Gaussian (8 adjacent lanes)
-#pragma unroll
-                        for (int o = 1; o < BWD_GROUPS; o <<= 1) {
-#pragma unroll
-                            for (int c = 0; c < CB; c++) dV[c] += __shfl_xor_sync(0xffffffffu, dV[c], o);
-#pragma unroll
-                            for (int d = 0; d < D; d++) dM[d] += __shfl_xor_sync(0xffffffffu, dM[d], o);
-#pragma unroll
-                            for (int k = 0; k < T; k++) dC[k] += __shfl_xor_sync(0xffffffffu, dC[k], o);
-                        }
-                        if (valid && grp == 0) {
-#pragma unroll
-                            for (int c = 0; c < CB; c++) atomicAdd(A.dvalues + (int64_t)gid * A.C + A.ch0 + c, dV[c]);
-#pragma unroll
-                            for (int d = 0; d < D; d++) atomicAdd(A.dmeans + (int64_t)gid * D + d, dM[d]);
-#pragma unroll
-                            for (int k = 0; k < T; k++) atomicAdd(A.dconics + (int64_t)gid * T + k, dC[k]);
-                        }
+                    for (int d = 0; d < D; d++) {
+                        const float m = __ldg(pr + d);
+                        const float xmin = m - hi[d], xmax = m - lo[d];
+                        if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;
+                        if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;
                     }
-                    staged = 0;
                 }
-                __syncthreads();
+                const uint32_t balP = __ballot_sync(0xffffffffu, pass);
+                const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
+                const uint32_t balG = balP & ~balF;
+                if (pass) {
+                    if (fast) qF[nf + __popc(balF & lt)] = id;
+                    else qG[ng + __popc(balG & lt)] = id | (exact ? BWD_EXACT_BIT : 0u);
+                }
+                nf += __popc(balF);
+                ng += __popc(balG);
+                const bool last = base + 32 >= g1;
+                __syncwarp();
+                if (nf >= 32 * NG) {
+                    bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane);
+                    const int rem = nf - 32 * NG;          // < 32
+                    uint32_t keep = 0;
+                    if (lane < rem) keep = qF[32 * NG + lane];
+                    __syncwarp();
+                    if (lane < rem) qF[lane] = keep;
+                    nf = rem;
+                    __syncwarp();
+                }
+                if (last && nf > 0) {
+                    if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane);
+                    else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane);
+                    nf = 0;
+                }
+                while (ng >= 32 || (last && ng > 0)) {
+                    const int cnt = ng < 32 ? ng : 32;
+                    bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, cnt, lane);
+                    const int rem = ng - cnt;          // < 32
+                    uint32_t keep = 0;
+                    if (lane < rem) keep = qG[32 + lane];
+                    __syncwarp();
+                    if (lane < rem) qG[lane] = keep;
+                    ng = rem;
+                    __syncwarp();
+                }
+                __syncwarp();
             }
         }
     }
 }
 
-float dgs_tau_for(const dgs_plan_t* plan, int fn);
-
-template <int D, int FN, int CB>
-static int bwd_launch_cb(const BwdArgs& a, int n_coarse, bool exact, cudaStream_t st) {
-    constexpr size_t smem = BwdLayout<D, FN, CB>::SMEM;
-    DGS_NOTE_LAUNCHES(1);
-    if (exact) {
-        auto k = dgs_backward_kernel<D, FN, CB, true>;
-        DGS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k<<<n_coarse, DGS_THREADS, smem, st>>>(a);
-    } else {
-        auto k = dgs_backward_kernel<D, FN, CB, false>;
-        DGS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k<<<n_coarse, DGS_THREADS, smem, st>>>(a);
-    }
-    return 0;
+// fn 0: raw moments -> gradients.  dmeans holds m1 = sum w X, dconics m2 = sum w X X^T (upper
+// triangle); dL/dmu = -C m1, dL/dC_ii = -m2_ii / 2, dL/dC_ij = -m2_ij (backward.cu:140-152),
+// times v when the weights were accumulated without it (VPOST).
+template <int D>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_bwd_finalize_kernel(const float* __restrict__ conics, const float* __restrict__ values,
+                                                                       int64_t P, int vpost, float* __restrict__ dmeans,
+                                                                       float* __restrict__ dconics) {
+    constexpr int T = D * (D + 1) / 2;
+    const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (i >= P) return;
+    float m1[D], m2[T], con[T];
+#pragma unroll
+    for (int d = 0; d < D; d++) m1[d] = dmeans[i * D + d];
+#pragma unroll
+    for (int k = 0; k < T; k++) { m2[k] = dconics[i * T + k]; con[k] = conics[i * T + k]; }
+    const float v = vpost ? values[i] : 1.0f;
+    float a[D];
+    dgs_conic_times<D>(con, m1, a);
+#pragma unroll
+    for (int d = 0; d < D; d++) dmeans[i * D + d] = -(v * a[d]);
+#pragma unroll
+    for (int m = 0; m < D; m++)
+#pragma unroll
+        for (int n = m; n < D; n++) dconics[i * T + dgs_tri(D, m, n)] = (m == n ? -0.5f : -1.0f) * v * m2[dgs_tri(D, m, n)];
 }
 
+float dgs_tau_for(const dgs_plan_t* plan, int fn);
+int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st);
+
 template <int D, int FN>
-static int bwd_launch_fn(BwdArgs a, int n_coarse, bool exact, cudaStream_t st) {
+static void bwd_launch_fn(BwdArgs a, int n_coarse, cudaStream_t st) {
     int ch = 0;
     while (ch < a.C) {
         const int left = a.C - ch;
         a.ch0 = ch;
-        int rc;
-        if (left >= 4) { rc = bwd_launch_cb<D, FN, 4>(a, n_coarse, exact, st); ch += 4; }
-        else if (left >= 2) { rc = bwd_launch_cb<D, FN, 2>(a, n_coarse, exact, st); ch += 2; }
-        else { rc = bwd_launch_cb<D, FN, 1>(a, n_coarse, exact, st); ch += 1; }
-        if (rc) return rc;
+        DGS_NOTE_LAUNCHES(1);
+        if (left >= 4) { dgs_backward_kernel<D, FN, 4, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 4; }
+        else if (left >= 2) { dgs_backward_kernel<D, FN, 2, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 2; }
+        else if (FN == 0 && a.C == 1) { dgs_backward_kernel<D, FN, 1, FN == 0><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 1; }
+        else { dgs_backward_kernel<D, FN, 1, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 1; }
     }
-    return 0;
 }
 
 template <int D>
-static int bwd_launch_d(const BwdArgs& a, int fn, int n_coarse, bool exact, cudaStream_t st) {
+static void bwd_launch_d(const BwdArgs& a, int fn, int n_coarse, int64_t P, cudaStream_t st) {
     switch (fn) {
-        case 0: return bwd_launch_fn<D, 0>(a, n_coarse, exact, st);
-        case 1: return bwd_launch_fn<D, 1>(a, n_coarse, exact, st);
-        case 2: return bwd_launch_fn<D, 2>(a, n_coarse, exact, st);
-        default: return bwd_launch_fn<D, 3>(a, n_coarse, exact, st);
+        case 0:
+            bwd_launch_fn<D, 0>(a, n_coarse, st);
+            dgs_bwd_finalize_kernel<D><<<dgs_cdiv(P, DGS_THREADS), DGS_THREADS, 0, st>>>(a.conics, a.values, P, a.C == 1 ? 1 : 0,
+                                                                                        a.dmeans, a.dconics);
+            DGS_NOTE_LAUNCHES(1);
+            break;
+        case 1: bwd_launch_fn<D, 1>(a, n_coarse, st); break;
+        case 2: bwd_launch_fn<D, 2>(a, n_coarse, st); break;
+        default: bwd_launch_fn<D, 3>(a, n_coarse, st); break;
     }
 }
 
 int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
-                        const float* conics, const float* dout, const uint8_t* gbuf, const uint8_t* sbuf,
+                        const float* conics, const float* dout, uint8_t* gbuf, const uint8_t* sbuf,
                         const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st) {
     (void)ranges;
     if (plan->N <= 0 || plan->n_coarse <= 0 || plan->P <= 0) return 0;
     BwdArgs a;
-    a.means = means; a.values = values; a.conics = conics; a.dout = dout;
+    a.values = values; a.conics = conics; a.dout = dout;
+    a.prec = (const float*)(gbuf + plan->g_prec_off);
     a.crec = (const DgsCullRec*)(gbuf + plan->g_crec_off);
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
@@ -351,12 +461,16 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     const float ratio = dgs_tau_for(plan, fn) / tau_max;
     a.shrink2 = ratio < 1.f ? ratio * 1.00002f : 1.f;
     a.shrink = ratio < 1.f ? sqrtf(ratio) * 1.00001f : 1.f;
-    const bool exact = plan->exact_wrap != 0;
-    int rc;
-    if (plan->D == 1) rc = bwd_launch_d<1>(a, fn, plan->n_coarse, exact, st);
-    else if (plan->D == 2) rc = bwd_launch_d<2>(a, fn, plan->n_coarse, exact, st);
-    else rc = bwd_launch_d<3>(a, fn, plan->n_coarse, exact, st);
+    const int T = plan->D * (plan->D + 1) / 2;
+    // the kernels accumulate: start from zero whatever the caller left in the buffers
+    DGS_CUDA(cudaMemsetAsync(dmeans, 0, (size_t)plan->P * plan->D * 4, st));
+    DGS_CUDA(cudaMemsetAsync(dvalues, 0, (size_t)plan->P * C * 4, st));
+    DGS_CUDA(cudaMemsetAsync(dconics, 0, (size_t)plan->P * T * 4, st));
+    int rc = dgs_launch_pack(means, conics, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
     if (rc) return rc;
+    if (plan->D == 1) bwd_launch_d<1>(a, fn, plan->n_coarse, plan->P, st);
+    else if (plan->D == 2) bwd_launch_d<2>(a, fn, plan->n_coarse, plan->P, st);
+    else bwd_launch_d<3>(a, fn, plan->n_coarse, plan->P, st);
     DGS_LAUNCH_CHECK();
     return 0;
 }

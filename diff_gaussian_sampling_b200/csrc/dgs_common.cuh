@@ -90,8 +90,8 @@ int dgs_sort_pairs_u32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_
 
 // --- kernels launched from dgs_api.cu ---------------------------------------------------
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
-                       const float* conics, const uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
+                       const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
                        float* out, unsigned long long* pair_counter, cudaStream_t st);
 int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
-                        const float* conics, const float* dout, const uint8_t* gbuf, const uint8_t* sbuf,
+                        const float* conics, const float* dout, uint8_t* gbuf, const uint8_t* sbuf,
                         const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st);

@@ -135,3 +135,85 @@ struct DgsPair {
         }
     }
 };
+
+// ---------------------------------------------------------------------------------------
+// Fast ("whitened") geometry.  For a positive-definite conic C the pack kernel (dgs_pack.cu)
+// stores the upper Cholesky factor U of (log2(e)/2) C, so that
+//     power * log2(e) = -|U X|^2        and        G = exp(power) = 2^-(|U X|^2).
+// No `power > 0` test is needed (|UX|^2 >= 0), and when no sample of the tile can have
+// |mu - x| > 1 the torus wrap (forward.cu:150-156) is the identity, so X = fl(mu - x) is the
+// reference's own value bit for bit.  D=2: 2 FADD + 5 FMUL/FFMA + 1 MUFU.EX2 per pair.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float dgs_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int D>
+__device__ __forceinline__ float dgs_white_G(const float* X, const float* U) {
+    float np;   // -|U X|^2
+    if (D == 1) {
+        const float y = U[0] * X[0];
+        np = -(y * y);
+    } else if (D == 2) {
+        const float y0 = fmaf(U[1], X[1], U[0] * X[0]);
+        const float y1 = U[2] * X[1];
+        np = fmaf(-y0, y0, -(y1 * y1));
+    } else {
+        const float y0 = fmaf(U[2], X[2], fmaf(U[1], X[1], U[0] * X[0]));
+        const float y1 = fmaf(U[4], X[2], U[3] * X[1]);
+        const float y2 = U[5] * X[2];
+        np = fmaf(-y0, y0, fmaf(-y1, y1, -(y2 * y2)));
+    }
+    return dgs_ex2(np);
+}
+
+// a = C X from the packed conic
+template <int D>
+__device__ __forceinline__ void dgs_conic_times(const float* con, const float* X, float* a) {
+#pragma unroll
+    for (int i = 0; i < D; i++) {
+        float s = con[dgs_tri_sym(D, i, 0)] * X[0];
+#pragma unroll
+        for (int j = 1; j < D; j++) s = fmaf(con[dgs_tri_sym(D, i, j)], X[j], s);
+        a[i] = s;
+    }
+}
+
+// unique components of the order-FN Hermite-like tensor from (a, C)
+template <int D, int FN>
+__device__ __forceinline__ void dgs_hermite(const float* a, const float* con, float* H) {
+    if (FN == 0) {
+        H[0] = 1.f;
+    } else if (FN == 1) {
+#pragma unroll
+        for (int i = 0; i < D; i++) H[i] = a[i];
+    } else if (FN == 2) {
+#pragma unroll
+        for (int i = 0; i < D; i++)
+#pragma unroll
+            for (int j = i; j < D; j++) H[dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
+    } else {
+        int u = 0;
+#pragma unroll
+        for (int i = 0; i < D; i++)
+#pragma unroll
+            for (int j = i; j < D; j++)
+#pragma unroll
+                for (int k = j; k < D; k++) {
+                    const float cij = con[dgs_tri(D, i, j)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, j, k)];
+                    float h = cij * a[k];
+                    h = fmaf(cik, a[j], h);
+                    h = fmaf(cjk, a[i], h);
+                    h = fmaf(-(a[i] * a[j]), a[k], h);
+                    H[u++] = h;
+                }
+    }
+}
+
+// Packed per-Gaussian record written by the pack kernel at every forward / backward call from
+// the call's own means and conics: mu[D], U[T] (see above), flags.  Stride DGS_PREC_W floats.
+#define DGS_PREC_W(D) ((D) == 3 ? 12 : 8)
+#define DGS_PREC_FAST 1u   // conic positive definite and finite: the whitened path is valid
+

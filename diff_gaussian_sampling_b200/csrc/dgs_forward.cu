@@ -3,21 +3,33 @@
 //
 // The reference launches ONE 256-thread CTA per 0.51-wide cell, walks every Gaussian of the
 // cell against every sample of the cell and does a global read-modify-write of the output per
-// pair and channel.  Here: one CTA per coarse tile (a sub-box of a reference cell).  For each
-// fine tile of <= ~256 samples the CTA streams the coarse tile's Gaussian list, keeps only the
-// Gaussians whose power >= -tau ellipsoid can reach the box of the samples actually in the
-// fine tile (everything else contributes < exp(-tau) of its peak), stages their parameters in
-// shared memory and lets every thread accumulate its own sample in registers — one coalesced
-// gather per surviving Gaussian per tile, smem-broadcast reads in the inner loop, one store per
-// output element.  Membership equals the reference's: only Gaussians the reference lists in the
-// cell are candidates.  Bound: FP32 issue (about 14 instructions + 1 MUFU.EX2 per pair).
+// pair and channel.  Here: one 4-warp CTA per coarse tile (a sub-box of a reference cell); every
+// WARP owns one fine tile (<= 32*S samples) at a time and works on it without any CTA barrier:
+//   1. each lane keeps up to S samples of the tile in registers (coordinates + accumulators);
+//   2. the warp streams the coarse tile's Gaussian list 32 candidates at a time, keeps the ones
+//      whose power >= -tau ellipsoid can reach the box of the samples actually in the tile (the
+//      rest contribute < exp(-tau) of their peak), and stages their packed records in its
+//      private shared-memory slice (ballot compaction);
+//   3. every staged record is read ONCE per lane (uniform shared-memory broadcast) and applied
+//      to the lane's S samples — the shared-memory return path, which bounds a one-sample-per-
+//      thread kernel, is amortised S-fold — with 2 FADD + 5 FMUL/FFMA + 1 MUFU.EX2 + 1 FFMA
+//      per pair for the 2D `gaussian` (whitened form, dgs_field.cuh);
+//   4. one store per output element.
+// Membership equals the reference's: only Gaussians the reference lists in the cell are
+// candidates.  Gaussians that need the torus wrap for some sample of the tile, or whose conic
+// is not positive definite, take the "general" path that restates forward.cu:147-184 literally.
+// Bound: FP32 pipe and MUFU.EX2 (8 lane-cycles each per pair and SM sub-partition in 2D).
 #include "dgs_field.cuh"
 #include "dgs_math.cuh"
 
-#define FWD_CAP 512   // staged Gaussians (shared memory records)
+#define FWD_WARPS 4
+#define FWD_THREADS (FWD_WARPS * 32)
+#define FWD_CAPF 64   // staged fast records per warp (flushed when more than CAPF-32 are waiting)
+#define FWD_CAPG 32   // staged general records per warp
 
 struct FwdArgs {
-    const float* means; const float* values; const float* conics;
+    const float* values; const float* conics;
+    const float* prec;
     const DgsCullRec* crec;
     const uint32_t* l1_start; const uint32_t* l1_ids;
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
@@ -29,29 +41,115 @@ struct FwdArgs {
     float shrink, shrink2;
 };
 
-template <int D, int CB>
-struct FwdRec {   // shared-memory record of a staged Gaussian
+template <int D, int FN, int CB>
+struct FwdCfg {
     static constexpr int T = D * (D + 1) / 2;
-    static constexpr int RAW = D + T + CB;
-    static constexpr int W = (RAW + 3) / 4 * 4;   // padded to 16 B
+    static constexpr int U = dgs_nuniq(D, FN);
+    static constexpr int AFULL = dgs_ipow(D, FN);
+    static constexpr int SMAX0 = 48 / (U * CB);
+    static constexpr int SMAX = SMAX0 < 1 ? 1 : (SMAX0 > 8 ? 8 : SMAX0);   // samples per lane
+    static constexpr int FW0 = D + T + (FN > 0 ? T : 0) + CB;              // mu | U | [conic] | v
+    static constexpr int FW = (FW0 + 1) / 2 * 2;
+    static constexpr int GW0 = D + T + CB + 1;                             // mu | conic | v | exact flag
+    static constexpr int GW = (GW0 + 1) / 2 * 2;
+    static constexpr int WARP_FLOATS = FWD_CAPF * FW + FWD_CAPG * GW;
 };
 
-template <int D, int FN, int CB, bool EXACT, bool COUNT_ONLY>
-__global__ void __launch_bounds__(DGS_THREADS) dgs_forward_kernel(const FwdArgs A) {
-    constexpr int T = D * (D + 1) / 2;
-    constexpr int U = dgs_nuniq(D, FN);
-    constexpr int AFULL = dgs_ipow(D, FN);
-    constexpr int W = FwdRec<D, CB>::W;
-    __shared__ __align__(16) float stage[FWD_CAP * W];
-    __shared__ uint32_t s_wc[DGS_THREADS / 32];
+template <int D, int FN, int CB, int S>
+__device__ __forceinline__ void fwd_eval_fast(const float* __restrict__ sF, int nf,
+                                              const float (&x)[FwdCfg<D, FN, CB>::SMAX][D],
+                                              float (&acc)[FwdCfg<D, FN, CB>::SMAX][FwdCfg<D, FN, CB>::U][CB]) {
+    using K = FwdCfg<D, FN, CB>;
+    constexpr int T = K::T, U = K::U, FW = K::FW;
+    for (int k = 0; k < nf; k++) {
+        float r[FW];
+#pragma unroll
+        for (int q = 0; q < FW / 2; q++) {
+            const float2 v = *(const float2*)(sF + k * FW + q * 2);
+            r[q * 2] = v.x; r[q * 2 + 1] = v.y;
+        }
+        const float* val = r + D + T + (FN > 0 ? T : 0);
+#pragma unroll
+        for (int i = 0; i < S; i++) {
+            float X[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) X[d] = r[d] - x[i][d];
+            const float G = dgs_white_G<D>(X, r + D);
+            if (FN == 0) {
+#pragma unroll
+                for (int c = 0; c < CB; c++) acc[i][0][c] = fmaf(val[c], G, acc[i][0][c]);
+            } else {
+                float a[D], H[U];
+                dgs_conic_times<D>(r + D + T, X, a);
+                dgs_hermite<D, FN>(a, r + D + T, H);
+#pragma unroll
+                for (int c = 0; c < CB; c++) {
+                    const float vg = val[c] * G;
+#pragma unroll
+                    for (int u = 0; u < U; u++) acc[i][u][c] = fmaf(vg, H[u], acc[i][u][c]);
+                }
+            }
+        }
+    }
+}
 
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+template <int D, int FN, int CB>
+__device__ __forceinline__ void fwd_eval_general(const float* __restrict__ sG, int ng, int s_eff,
+                                                 const float (&x)[FwdCfg<D, FN, CB>::SMAX][D],
+                                                 float (&acc)[FwdCfg<D, FN, CB>::SMAX][FwdCfg<D, FN, CB>::U][CB]) {
+    using K = FwdCfg<D, FN, CB>;
+    constexpr int T = K::T, U = K::U, GW = K::GW, GW0 = K::GW0, SMAX = K::SMAX;
+    for (int k = 0; k < ng; k++) {
+        float r[GW];
+#pragma unroll
+        for (int q = 0; q < GW / 2; q++) {
+            const float2 v = *(const float2*)(sG + k * GW + q * 2);
+            r[q * 2] = v.x; r[q * 2 + 1] = v.y;
+        }
+        const bool exact = r[GW0 - 1] != 0.f;
+#pragma unroll
+        for (int i = 0; i < SMAX; i++) {
+            if (i < s_eff) {
+                float H[U], G;
+                if (exact) {
+                    DgsPair<D, FN, true> p;
+                    p.eval(x[i], r, r + D);
+                    p.hermite(r + D, H);
+                    G = p.G;
+                } else {
+                    DgsPair<D, FN, false> p;
+                    p.eval(x[i], r, r + D);
+                    p.hermite(r + D, H);
+                    G = p.G;
+                }
+#pragma unroll
+                for (int c = 0; c < CB; c++) {
+                    const float vg = r[D + T + c] * G;
+#pragma unroll
+                    for (int u = 0; u < U; u++) acc[i][u][c] = (FN == 0) ? acc[i][u][c] + vg : fmaf(vg, H[u], acc[i][u][c]);
+                }
+            }
+        }
+    }
+}
+
+template <int D, int FN, int CB, bool COUNT_ONLY>
+__global__ void __launch_bounds__(FWD_THREADS) dgs_forward_kernel(const FwdArgs A) {
+    using K = FwdCfg<D, FN, CB>;
+    constexpr int T = K::T, U = K::U, AFULL = K::AFULL, SMAX = K::SMAX, FW = K::FW, GW = K::GW, GW0 = K::GW0;
+    constexpr int PW = DGS_PREC_W(D);
+    __shared__ __align__(16) float smem[COUNT_ONLY ? 4 : FWD_WARPS * K::WARP_FLOATS];
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    float* sF = smem + (COUNT_ONLY ? 0 : warp * K::WARP_FLOATS);
+    float* sG = sF + (COUNT_ONLY ? 0 : FWD_CAPF * FW);
     const int64_t coarse = blockIdx.x;
     if (__float_as_int(A.coarse_aabb[coarse * 8 + 6]) == 0) return;   // no samples here
     const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
     unsigned long long pairs = 0;
 
-    for (int ft = 0; ft < A.fpcD; ft++) {
+    for (int ft = warp; ft < A.fpcD; ft += FWD_WARPS) {
         const int64_t tile = coarse * A.fpcD + ft;
         const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
         if (s0 == s1) continue;
@@ -61,133 +159,163 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_forward_kernel(const FwdArgs 
             const float4 b1 = *(const float4*)(A.fine_aabb + tile * 8 + 4);
             lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b0.w; hi[1] = b1.x; hi[2] = b1.y;
         }
-        for (uint32_t sb = s0; sb < s1; sb += DGS_THREADS) {
-            const uint32_t j = sb + tid;
-            const bool active = j < s1;
-            float x[D];
-            uint32_t sid = 0;
+        // balanced passes of at most 32*SMAX samples
+        const uint32_t n = s1 - s0;
+        const uint32_t n_pass = (n + 32 * SMAX - 1) / (32 * SMAX);
+        const uint32_t per = (n + n_pass - 1) / n_pass;
+        const int s_eff = (int)((per + 31) / 32);
+        for (uint32_t pb = s0; pb < s1; pb += (uint32_t)s_eff * 32) {
+            const uint32_t pe = min(s1, pb + (uint32_t)s_eff * 32);
+            float x[SMAX][D];
+            float acc[SMAX][U][CB];
 #pragma unroll
-            for (int d = 0; d < D; d++) x[d] = active ? A.fine_xyz[(int64_t)d * A.N + j] : 0.f;
-            if (active) sid = A.fine_ids[j];
-            float acc[U][CB];
+            for (int i = 0; i < SMAX; i++) {
+                const uint32_t j = pb + (uint32_t)i * 32 + lane;
+                const bool act = (i < s_eff) && (j < pe);
 #pragma unroll
-            for (int u = 0; u < U; u++)
+                for (int d = 0; d < D; d++) x[i][d] = (act && !COUNT_ONLY) ? A.fine_xyz[(int64_t)d * A.N + j] : 0.f;
 #pragma unroll
-                for (int c = 0; c < CB; c++) acc[u][c] = 0.f;
+                for (int u = 0; u < U; u++)
+#pragma unroll
+                    for (int c = 0; c < CB; c++) acc[i][u][c] = 0.f;
+            }
 
-            uint32_t staged = 0;
-            for (uint32_t base = g0; base < g1; base += DGS_THREADS) {
-                const uint32_t e = base + tid;
-                bool pass = false;
+            int nf = 0, ng = 0;
+            for (uint32_t base = g0; base < g1; base += 32) {
+                const uint32_t e = base + lane;
+                bool pass = false, fast = false, exact = false;
                 uint32_t id = 0;
+                float pr[PW];
                 if (e < g1) {
                     id = A.l1_ids[e];
                     const DgsCullRec rec = A.crec[id];
                     pass = dgs_cull_pass<D>(rec, lo, hi, A.shrink, A.shrink2);
                 }
-                const uint32_t bal = __ballot_sync(0xffffffffu, pass);
-                if (lane == 0) s_wc[w] = __popc(bal);
-                __syncthreads();
-                uint32_t pre = 0, tot = 0;
-#pragma unroll
-                for (int k = 0; k < DGS_THREADS / 32; k++) {
-                    const uint32_t c = s_wc[k];
-                    pre += (k < w) ? c : 0u;
-                    tot += c;
-                }
                 if (pass && !COUNT_ONLY) {
-                    float* r = stage + (size_t)(staged + pre + __popc(bal & ((1u << lane) - 1u))) * W;
+                    const float4* p4 = (const float4*)(A.prec + (int64_t)id * PW);
 #pragma unroll
-                    for (int d = 0; d < D; d++) r[d] = A.means[(int64_t)id * D + d];
-#pragma unroll
-                    for (int k = 0; k < T; k++) r[D + k] = A.conics[(int64_t)id * T + k];
-#pragma unroll
-                    for (int c = 0; c < CB; c++) r[D + T + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
-                }
-                staged += tot;
-                const bool last = base + DGS_THREADS >= g1;
-                if (staged > FWD_CAP - DGS_THREADS || last) {
-                    __syncthreads();
-                    if (COUNT_ONLY) {
-                        if (active) pairs += staged;
-                    } else if (active) {
-                        for (uint32_t k = 0; k < staged; k++) {
-                            float r[W];
-#pragma unroll
-                            for (int q = 0; q < W / 4; q++) {
-                                const float4 v = *(const float4*)(stage + (size_t)k * W + q * 4);
-                                r[q * 4 + 0] = v.x; r[q * 4 + 1] = v.y; r[q * 4 + 2] = v.z; r[q * 4 + 3] = v.w;
-                            }
-                            DgsPair<D, FN, EXACT> p;
-                            p.eval(x, r, r + D);
-                            float H[U];
-                            p.hermite(r + D, H);
-#pragma unroll
-                            for (int c = 0; c < CB; c++) {
-                                const float vg = r[D + T + c] * p.G;
-#pragma unroll
-                                for (int u = 0; u < U; u++) acc[u][c] = (FN == 0) ? acc[u][c] + vg : fmaf(vg, H[u], acc[u][c]);
-                            }
-                        }
+                    for (int q = 0; q < PW / 4; q++) {
+                        const float4 v = __ldg(p4 + q);
+                        pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
                     }
-                    staged = 0;
+                    fast = (__float_as_uint(pr[PW - 1]) & DGS_PREC_FAST) != 0u;
+#pragma unroll
+                    for (int d = 0; d < D; d++) {
+                        // fp32 subtraction is monotone: every sample of the tile has fl(mu - x) in [xmin, xmax]
+                        const float xmin = pr[d] - hi[d], xmax = pr[d] - lo[d];
+                        if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;            // some sample wraps (forward.cu:150)
+                        if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;  // fmod arm differs from -/+ 2
+                    }
                 }
-                __syncthreads();
+                const uint32_t balP = __ballot_sync(0xffffffffu, pass);
+                if (COUNT_ONLY) {
+                    pairs += (unsigned long long)__popc(balP) * (pe - pb);
+                    continue;
+                }
+                const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
+                const uint32_t balG = balP & ~balF;
+                if (pass) {
+                    if (fast) {
+                        float* r = sF + (nf + __popc(balF & lt)) * FW;
+#pragma unroll
+                        for (int q = 0; q < D + T; q++) r[q] = pr[q];
+                        if (FN > 0) {
+#pragma unroll
+                            for (int k = 0; k < T; k++) r[D + T + k] = A.conics[(int64_t)id * T + k];
+                        }
+#pragma unroll
+                        for (int c = 0; c < CB; c++) r[D + T + (FN > 0 ? T : 0) + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
+                    } else {
+                        float* r = sG + (ng + __popc(balG & lt)) * GW;
+#pragma unroll
+                        for (int d = 0; d < D; d++) r[d] = pr[d];
+#pragma unroll
+                        for (int k = 0; k < T; k++) r[D + k] = A.conics[(int64_t)id * T + k];
+#pragma unroll
+                        for (int c = 0; c < CB; c++) r[D + T + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
+                        r[GW0 - 1] = exact ? 1.f : 0.f;
+                    }
+                }
+                nf += __popc(balF);
+                ng += __popc(balG);
+                const bool last = base + 32 >= g1;
+                __syncwarp();
+                if (nf > FWD_CAPF - 32 || (last && nf > 0)) {
+                    switch (s_eff) {
+                        case 1: fwd_eval_fast<D, FN, CB, 1>(sF, nf, x, acc); break;
+                        case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1>(sF, nf, x, acc); break;
+                        case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1>(sF, nf, x, acc); break;
+                        case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1>(sF, nf, x, acc); break;
+                        case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1>(sF, nf, x, acc); break;
+                        case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1>(sF, nf, x, acc); break;
+                        case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1>(sF, nf, x, acc); break;
+                        default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1>(sF, nf, x, acc); break;
+                    }
+                    nf = 0;
+                }
+                if (ng > FWD_CAPG - 32 || (last && ng > 0)) {
+                    fwd_eval_general<D, FN, CB>(sG, ng, s_eff, x, acc);
+                    ng = 0;
+                }
+                __syncwarp();
             }
-            if (active && !COUNT_ONLY) {
-                float* o = A.out + (int64_t)sid * AFULL * A.C + A.ch0;
+            if (!COUNT_ONLY) {
 #pragma unroll
-                for (int al = 0; al < AFULL; al++)
+                for (int i = 0; i < SMAX; i++) {
+                    const uint32_t j = pb + (uint32_t)i * 32 + lane;
+                    if ((i < s_eff) && (j < pe)) {
+                        const uint32_t sid = A.fine_ids[j];
+                        float* o = A.out + (int64_t)sid * AFULL * A.C + A.ch0;
 #pragma unroll
-                    for (int c = 0; c < CB; c++) o[(int64_t)al * A.C + c] = acc[dgs_uniq_of(D, FN, al)][c];
+                        for (int al = 0; al < AFULL; al++)
+#pragma unroll
+                            for (int c = 0; c < CB; c++) o[(int64_t)al * A.C + c] = acc[i][dgs_uniq_of(D, FN, al)][c];
+                    }
+                }
             }
         }
     }
     if (COUNT_ONLY) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) pairs += __shfl_xor_sync(0xffffffffu, pairs, o);
+        // every lane carries the same per-warp count
         if (lane == 0 && pairs) atomicAdd(A.pair_counter, pairs);
     }
 }
 
 float dgs_tau_for(const dgs_plan_t* plan, int fn) { return plan->tau + DGS_TAU_STEP * (float)fn; }
 
-template <int D, int FN, int CB>
-static void fwd_launch_cb(const FwdArgs& a, int n_coarse, bool exact, cudaStream_t st) {
-    DGS_NOTE_LAUNCHES(1);
-    if (exact) dgs_forward_kernel<D, FN, CB, true, false><<<n_coarse, DGS_THREADS, 0, st>>>(a);
-    else dgs_forward_kernel<D, FN, CB, false, false><<<n_coarse, DGS_THREADS, 0, st>>>(a);
-}
-
 template <int D, int FN>
-static void fwd_launch_fn(FwdArgs a, int n_coarse, bool exact, cudaStream_t st) {
+static void fwd_launch_fn(FwdArgs a, int n_coarse, cudaStream_t st) {
     int ch = 0;
     while (ch < a.C) {
         const int left = a.C - ch;
         a.ch0 = ch;
-        if (left >= 4) { fwd_launch_cb<D, FN, 4>(a, n_coarse, exact, st); ch += 4; }
-        else if (left >= 2) { fwd_launch_cb<D, FN, 2>(a, n_coarse, exact, st); ch += 2; }
-        else { fwd_launch_cb<D, FN, 1>(a, n_coarse, exact, st); ch += 1; }
+        DGS_NOTE_LAUNCHES(1);
+        if (left >= 4) { dgs_forward_kernel<D, FN, 4, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 4; }
+        else if (left >= 2) { dgs_forward_kernel<D, FN, 2, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 2; }
+        else { dgs_forward_kernel<D, FN, 1, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 1; }
     }
 }
 
 template <int D>
-static void fwd_launch_d(const FwdArgs& a, int fn, int n_coarse, bool exact, cudaStream_t st) {
+static void fwd_launch_d(const FwdArgs& a, int fn, int n_coarse, cudaStream_t st) {
     switch (fn) {
-        case 0: fwd_launch_fn<D, 0>(a, n_coarse, exact, st); break;
-        case 1: fwd_launch_fn<D, 1>(a, n_coarse, exact, st); break;
-        case 2: fwd_launch_fn<D, 2>(a, n_coarse, exact, st); break;
-        default: fwd_launch_fn<D, 3>(a, n_coarse, exact, st); break;
+        case 0: fwd_launch_fn<D, 0>(a, n_coarse, st); break;
+        case 1: fwd_launch_fn<D, 1>(a, n_coarse, st); break;
+        case 2: fwd_launch_fn<D, 2>(a, n_coarse, st); break;
+        default: fwd_launch_fn<D, 3>(a, n_coarse, st); break;
     }
 }
 
+int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st);
+
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
-                       const float* conics, const uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
+                       const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
                        float* out, unsigned long long* pair_counter, cudaStream_t st) {
     (void)ranges;
     if (plan->N <= 0 || plan->n_coarse <= 0) return 0;
     FwdArgs a;
-    a.means = means; a.values = values; a.conics = conics;
+    a.values = values; a.conics = conics;
+    a.prec = (const float*)(gbuf + plan->g_prec_off);
     a.crec = (const DgsCullRec*)(gbuf + plan->g_crec_off);
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
@@ -202,14 +330,19 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     const float ratio = dgs_tau_for(plan, fn) / tau_max;
     a.shrink2 = ratio < 1.f ? ratio * 1.00002f : 1.f;
     a.shrink = ratio < 1.f ? sqrtf(ratio) * 1.00001f : 1.f;
-    const bool exact = plan->exact_wrap != 0;
     if (pair_counter) {
-        if (plan->D == 1) dgs_forward_kernel<1, 0, 1, false, true><<<plan->n_coarse, DGS_THREADS, 0, st>>>(a);
-        else if (plan->D == 2) dgs_forward_kernel<2, 0, 1, false, true><<<plan->n_coarse, DGS_THREADS, 0, st>>>(a);
-        else dgs_forward_kernel<3, 0, 1, false, true><<<plan->n_coarse, DGS_THREADS, 0, st>>>(a);
-    } else if (plan->D == 1) fwd_launch_d<1>(a, fn, plan->n_coarse, exact, st);
-    else if (plan->D == 2) fwd_launch_d<2>(a, fn, plan->n_coarse, exact, st);
-    else fwd_launch_d<3>(a, fn, plan->n_coarse, exact, st);
+        DGS_NOTE_LAUNCHES(1);
+        if (plan->D == 1) dgs_forward_kernel<1, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);
+        else if (plan->D == 2) dgs_forward_kernel<2, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);
+        else dgs_forward_kernel<3, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);
+        DGS_LAUNCH_CHECK();
+        return 0;
+    }
+    int rc = dgs_launch_pack(means, conics, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
+    if (rc) return rc;
+    if (plan->D == 1) fwd_launch_d<1>(a, fn, plan->n_coarse, st);
+    else if (plan->D == 2) fwd_launch_d<2>(a, fn, plan->n_coarse, st);
+    else fwd_launch_d<3>(a, fn, plan->n_coarse, st);
     DGS_LAUNCH_CHECK();
     return 0;
 }

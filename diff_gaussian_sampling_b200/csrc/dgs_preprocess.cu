@@ -526,9 +526,15 @@ int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const ui
 // samples actually in t can reach power >= -tau_max.  EMIT=false counts, EMIT=true writes
 // (tile, g) pairs in ascending g; a stable sort by tile then yields ascending-g lists.
 // ------------------------------------------------------------------------------------
+//
+// Only the coarse tiles whose NOMINAL extent (cell c, tile t: (s - off)/0.51 in c + [t, t+1]/T1, plus a
+// slop that covers the fp32 rounding of dgs_sample_cell / dgs_fine_coord) can reach the Gaussian's
+// tau box, or one of its period-2 images, are visited; the decision itself is always taken on the
+// bounding box of the samples actually in the tile.
 template <int D, bool EMIT>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __restrict__ means, const float* __restrict__ radii,
                                                              const DgsCullRec* __restrict__ crec, int64_t P, DgsGrid G, int cpc,
+                                                             int T1, int blocks,
                                                              const float* __restrict__ coarse_aabb, uint32_t* __restrict__ n1,
                                                              const uint32_t* __restrict__ n1_off, uint32_t* __restrict__ keys,
                                                              uint32_t* __restrict__ vals) {
@@ -542,19 +548,53 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         for (int k = 0; k < D; k++) p[k] = means[i * D + k];
         const DgsCullRec rec = crec[i];
         uint32_t o = EMIT ? n1_off[i] : 0u;
+        auto test_tile = [&](int64_t tile) {
+            const float4 a = __ldg((const float4*)(coarse_aabb + tile * 8));
+            const float4 b = __ldg((const float4*)(coarse_aabb + tile * 8) + 1);
+            const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
+            if (!(lo[0] <= hi[0])) return;   // no samples in this tile
+            if (dgs_cull_pass<D>(rec, lo, hi, 1.0f, 1.0f)) {
+                if (EMIT) { keys[o] = (uint32_t)tile; vals[o] = (uint32_t)i; o++; }
+                cnt++;
+            }
+        };
         dgs_for_each_cell<D>(p, r, G, [&](int cell) {
             if (cell >= G.n_ranges) return;
             const int64_t t0 = (int64_t)cell * cpc;
-            for (int t = 0; t < cpc; t++) {
-                const float4 a = __ldg((const float4*)(coarse_aabb + (t0 + t) * 8));
-                const float4 b = __ldg((const float4*)(coarse_aabb + (t0 + t) * 8) + 1);
-                const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
-                if (!(lo[0] <= hi[0])) continue;   // no samples in this tile
-                if (dgs_cull_pass<D>(rec, lo, hi, 1.0f, 1.0f)) {
-                    if (EMIT) { keys[o] = (uint32_t)(t0 + t); vals[o] = (uint32_t)i; o++; }
-                    cnt++;
-                }
+            if ((rec.flags & DGS_CREC_ALWAYS) || cell >= blocks || T1 < 3) {
+                for (int t = 0; t < cpc; t++) test_tile(t0 + t);
+                return;
             }
+            int cc[3] = {0, 0, 0};
+            cc[0] = cell % G.g[0];
+            if (D > 1) cc[1] = (cell / G.g[0]) % G.g[1];
+            if (D > 2) cc[2] = cell / (G.g[0] * G.g[1]);
+            int tlo[3] = {0, 0, 0}, thi[3] = {0, 0, 0};
+            bool any = true;
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                int lo_t = T1, hi_t = -1;
+#pragma unroll
+                for (int k = -1; k <= 1; k++) {
+                    const float m = rec.mu[d] + 2.0f * (float)k - G.off[d];
+                    const float qa = (m - rec.R[d]) / DGS_CELL - (float)cc[d];
+                    const float qb = (m + rec.R[d]) / DGS_CELL - (float)cc[d];
+                    const float slop = 2e-5f + 2e-6f * (fabsf(qa) + fabsf(qb) + (float)cc[d]);
+                    const float fa = floorf((qa - slop) * (float)T1) - 1.f;
+                    const float fb = floorf((qb + slop) * (float)T1) + 1.f;
+                    if (fb < 0.f || fa > (float)(T1 - 1)) continue;   // this image misses the cell
+                    const int ia = fa < 0.f ? 0 : (int)fa;
+                    const int ib = fb > (float)(T1 - 1) ? T1 - 1 : (int)fb;
+                    lo_t = ia < lo_t ? ia : lo_t;
+                    hi_t = ib > hi_t ? ib : hi_t;
+                }
+                tlo[d] = lo_t; thi[d] = hi_t;
+                any = any && (lo_t <= hi_t);
+            }
+            if (!any) return;
+            for (int tz = tlo[2]; tz <= thi[2]; tz++)
+                for (int ty = tlo[1]; ty <= thi[1]; ty++)
+                    for (int tx = tlo[0]; tx <= thi[0]; tx++) test_tile(t0 + ((int64_t)tz * T1 + ty) * T1 + tx);
         });
     }
     if (!EMIT) n1[i] = cnt;
@@ -570,8 +610,8 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const DgsCu
     const int nb = dgs_cdiv(P, DGS_THREADS);
     const int cpc = plan->coarse_per_cell;
 #define L1_LAUNCH(DD)                                                                                                         \
-    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, coarse_aabb, n1, n1_off, keys, vals); \
-    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, coarse_aabb, n1, n1_off, keys, vals);
+    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals); \
+    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals);
     if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
 #undef L1_LAUNCH
     DGS_NOTE_LAUNCHES(1);

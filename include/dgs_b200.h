@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define DGS_ABI_VERSION 2
+#define DGS_ABI_VERSION 3
 #define DGS_ERR_BAD_ARG 10001
 #define DGS_ERR_UNSUPPORTED 10002
 #define DGS_ERR_BUFFER_TOO_SMALL 10003
@@ -90,7 +90,8 @@ typedef struct dgs_plan {
     uint64_t g_plan_off, g_crec_off, g_l1_start_off, g_l1_ids_off, g_sort_tmp_off;
     uint64_t s_plan_off, s_fine_start_off, s_fine_ids_off, s_fine_xyz_off, s_fine_aabb_off,
              s_coarse_aabb_off, s_tmp_off;
-    int32_t  reserved[8];
+    uint64_t g_prec_off;           /* per-call packed Gaussian records (written by forward/backward) */
+    int32_t  reserved[6];
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
@@ -159,24 +160,28 @@ int dgs_plan_from_buffer(const void* binning_dev, size_t binning_bytes, uint32_t
  * sample_gaussians / _derivative / _laplacian / _third_derivative forward
  * (reference: SampleGaussians*CUDA, sample_points.cu:100-143,198-297; kernels forward.cu:87-275).
  * out_dev: (N, D^fn, C) fp32; every element is written (the reference zero-fills and
- * accumulates, sample_points.cu:215).  Asynchronous.
+ * accumulates, sample_points.cu:215).  Asynchronous.  means/conics/values are read as given at
+ * this call (like the reference); the call re-packs them into a scratch region of binning_dev
+ * (hence non-const), so calls that share one binning buffer must be stream-ordered.  The
+ * tau-culling uses the means/conics seen by preprocess: they must not have moved since.
  */
 int dgs_sample_forward(const dgs_plan_t* plan, int fn, int C,
                        const float* means_dev, const float* values_dev, const float* conics_dev,
                        const float* samples_dev,
-                       const void* binning_dev, const void* sample_binning_dev,
+                       void* binning_dev, const void* sample_binning_dev,
                        const void* ranges_dev, const void* sample_ranges_dev,
                        float* out_dev, void* stream);
 
 /*
  * Backward of the above (reference: SampleGaussians*BackwardCUDA, sample_points.cu:145-196,
  * 299-372; kernels backward.cu:26-416).  dmeans (P,D), dvalues (P,C), dconics (P,D(D+1)/2)
- * zero-filled by the caller (sample_points.cu:165-167); results are accumulated into them.
+ * are overwritten (the reference allocates them zero-filled, sample_points.cu:165-167, and
+ * accumulates with atomics).  Asynchronous.
  */
 int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C,
                         const float* means_dev, const float* values_dev, const float* conics_dev,
                         const float* samples_dev, const float* dout_dev,
-                        const void* binning_dev, const void* sample_binning_dev,
+                        void* binning_dev, const void* sample_binning_dev,
                         const void* ranges_dev, const void* sample_ranges_dev,
                         float* dmeans_dev, float* dvalues_dev, float* dconics_dev, void* stream);
 

@@ -32,6 +32,8 @@ def test_fields_and_grads_vs_reference_golden(name):
     for f in parity.FN:
         e = parity.fwd_err(got["out_" + f], g["out_" + f].astype(np.float64), orc["abs_" + f])
         assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
+        e = parity.norm_err(got["out_" + f], g["out_" + f].astype(np.float64))
+        assert e <= parity.FWD_RTOL, f"{name} {f} forward normwise err {e:.2e}"
         for k in ("dmeans_", "dvalues_", "dconics_"):
             e = parity.bwd_err(got[k + f], g[k + f].astype(np.float64))
             assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
@@ -46,6 +48,8 @@ def test_everything_vs_cpu_oracle(name):
     for f in parity.FN:
         e = parity.fwd_err(got["out_" + f], orc["out_" + f], orc["abs_" + f])
         assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
+        e = parity.norm_err(got["out_" + f], orc["out_" + f])
+        assert e <= parity.FWD_RTOL, f"{name} {f} forward normwise err {e:.2e}"
         for k in ("dmeans_", "dvalues_", "dconics_"):
             e = parity.bwd_err(got[k + f], orc[k + f])
             assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
