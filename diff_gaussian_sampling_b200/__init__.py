@@ -193,10 +193,102 @@ class _NativeOps:
 
     # -- aggregate_neighbors (aggregate_neighbors.cu:323-475): SURVEY.md §8 rows a-16..a-19 --
     @staticmethod
-    def preprocess_aggregate(*a):
-        raise NotImplementedError("aggregate_neighbors is not built yet in libdgs_b200 (SURVEY.md §8 a-16..a-19)")
-    aggregate_neighbors = preprocess_aggregate
-    aggregate_neighbors_backward = preprocess_aggregate
+    def preprocess_aggregate(means, conics, radii, debug):
+        """AggregateNeighborsPreprocessCUDA (aggregate_neighbors.cu:323-367) ->
+        (indices i64, ranges i64 inclusive cumsum, dists (len,D), densities (len), inv_total_densities (P))."""
+        lib = _lib.load()
+        means = _f32c(means, "means"); conics = _f32c(conics, "conics"); radii = _f32c(radii, "radii")
+        P, D = means.shape[0], means.shape[-1]
+        dev = means.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        i64 = dict(dtype=torch.int64, device=dev)
+        if P == 0:
+            return (torch.empty(0, **i64), torch.empty(0, **i64), torch.empty(0, D, **f32), torch.empty(0, **f32),
+                    torch.empty(0, **f32))
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream().cuda_stream
+            ws = torch.empty(lib.dgs_aggregate_ws_bytes(P, D), dtype=torch.uint8, device=dev)
+            ranges = torch.empty(P, **i64)
+            length = ctypes.c_longlong(0)
+            _lib.check(lib.dgs_aggregate_count(means.data_ptr(), radii.data_ptr(), P, D, ws.data_ptr(), ws.numel(),
+                                               ranges.data_ptr(), ctypes.byref(length), st), "dgs_aggregate_count")
+            n = int(length.value)
+            indices = torch.empty(n, **i64)
+            dists = torch.empty(n, D, **f32)
+            densities = torch.empty(n, **f32)
+            inv_total = torch.empty(P, **f32)
+            _lib.check(lib.dgs_aggregate_fill(means.data_ptr(), conics.data_ptr(), radii.data_ptr(), P, D, ws.data_ptr(),
+                                              ws.numel(), ranges.data_ptr(), n, indices.data_ptr(), dists.data_ptr(),
+                                              densities.data_ptr(), inv_total.data_ptr(), st), "dgs_aggregate_fill")
+            if debug:
+                torch.cuda.synchronize(dev)
+        return indices, ranges, dists, densities, inv_total
+
+    @staticmethod
+    def _agg_dims(features, queries, frequencies, distance_transform, dists):
+        return (features.shape[0], dists.shape[-1], features.shape[-1], queries.shape[-1],
+                distance_transform.shape[-1] // 2, frequencies.shape[0])
+
+    @staticmethod
+    def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform,
+                            indices, ranges, dists, densities, inv_total_densities, debug):
+        """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415) -> (weights, embeddings, factors, neighbor_features)."""
+        lib = _lib.load()
+        features = _f32c(features, "features"); transform = _f32c(transform, "transform")
+        queries = _f32c(queries, "queries"); keys = _f32c(keys, "keys")
+        frequencies = _f32c(frequencies, "frequencies"); distance_transform = _f32c(distance_transform, "distance_transform")
+        dists = _f32c(dists, "dists"); densities = _f32c(densities, "densities")
+        inv_total_densities = _f32c(inv_total_densities, "inv_total_densities")
+        indices = indices.contiguous(); ranges = ranges.contiguous()
+        P, D, L, K, E, nfq = _NativeOps._agg_dims(features, queries, frequencies, distance_transform, dists)
+        dev = features.device
+        n = densities.shape[0]
+        weights = torch.empty(n, dtype=torch.float32, device=dev)
+        embeddings = torch.empty_like(weights)
+        factors = torch.empty_like(weights)
+        out = torch.zeros(P, L, dtype=torch.float32, device=dev)
+        if P == 0:
+            return weights, embeddings, factors, out
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_aggregate_forward(P, D, L, K, E, nfq, features.data_ptr(), transform.data_ptr(),
+                                                 queries.data_ptr(), keys.data_ptr(), frequencies.data_ptr(),
+                                                 distance_transform.data_ptr(), indices.data_ptr(), ranges.data_ptr(),
+                                                 dists.data_ptr(), densities.data_ptr(), inv_total_densities.data_ptr(),
+                                                 weights.data_ptr(), embeddings.data_ptr(), factors.data_ptr(),
+                                                 out.data_ptr(), st), "dgs_aggregate_forward")
+            if debug:
+                torch.cuda.synchronize(dev)
+        return weights, embeddings, factors, out
+
+    @staticmethod
+    def aggregate_neighbors_backward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges,
+                                     dists, densities, weights, embeddings, factors, inv_total_densities, grad_out, debug):
+        """AggregateNeighborsBackwardCUDA (aggregate_neighbors.cu:417-475) -> grads of (features, transform, queries,
+        keys, frequencies, distance_transform)."""
+        lib = _lib.load()
+        features = _f32c(features, "features"); transform = _f32c(transform, "transform")
+        queries = _f32c(queries, "queries"); keys = _f32c(keys, "keys")
+        frequencies = _f32c(frequencies, "frequencies"); distance_transform = _f32c(distance_transform, "distance_transform")
+        grad_out = _f32c(grad_out, "dL_dneighbor_features")
+        dists = dists.contiguous(); indices = indices.contiguous(); ranges = ranges.contiguous()
+        P, D, L, K, E, nfq = _NativeOps._agg_dims(features, queries, frequencies, distance_transform, dists)
+        z = lambda t: torch.zeros_like(t)
+        grads = (z(features), z(transform), z(queries), z(keys), z(frequencies), z(distance_transform))
+        if P == 0:
+            return grads
+        with torch.cuda.device(features.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_aggregate_backward(
+                P, D, L, K, E, nfq, features.data_ptr(), transform.data_ptr(), queries.data_ptr(), keys.data_ptr(),
+                frequencies.data_ptr(), distance_transform.data_ptr(), indices.data_ptr(), ranges.data_ptr(),
+                dists.data_ptr(), densities.contiguous().data_ptr(), weights.contiguous().data_ptr(),
+                embeddings.contiguous().data_ptr(), factors.contiguous().data_ptr(),
+                inv_total_densities.contiguous().data_ptr(), grad_out.data_ptr(), *[g.data_ptr() for g in grads], st),
+                "dgs_aggregate_backward")
+            if debug:
+                torch.cuda.synchronize(features.device)
+        return grads
 
 
 _C = _NativeOps

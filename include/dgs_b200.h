@@ -191,6 +191,43 @@ int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C,
 int dgs_count_pairs(const dgs_plan_t* plan, int fn, const void* binning_dev, const void* sample_binning_dev,
                     unsigned long long* counter_dev, void* stream);
 
+/*
+ * ---- aggregate_neighbors (reference: aggregate_neighbors.cu / aggregate_neighbors.h:11-47) ----
+ * preprocess_aggregate is two-phase because the CSR length is data dependent (the reference
+ * syncs on ranges[-1].item<int>(), aggregate_neighbors.cu:345):
+ *   dgs_aggregate_ws_bytes -> caller allocates the workspace
+ *   dgs_aggregate_count    -> ranges (int64 inclusive cumsum, P entries) + CSR length on the host
+ *                             (replaces findCollisions :18-55 and the P x P bool tensor :332-345)
+ *   dgs_aggregate_fill     -> indices (int64, -1 holes) / dists (length,D) / densities (length) /
+ *                             inv_total_densities (P)      (replaces preprocess :57-127)
+ * The workspace must stay untouched between count and fill.
+ */
+size_t dgs_aggregate_ws_bytes(int64_t P, int D);
+int dgs_aggregate_count(const float* means_dev, const float* radii_dev, int64_t P, int D, void* ws_dev,
+                        size_t ws_bytes, long long* ranges_dev, long long* length_host, void* stream);
+int dgs_aggregate_fill(const float* means_dev, const float* conics_dev, const float* radii_dev, int64_t P, int D,
+                       void* ws_dev, size_t ws_bytes, const long long* ranges_dev, long long length,
+                       long long* indices_dev, float* dists_dev, float* densities_dev, float* inv_total_dev,
+                       void* stream);
+/* AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415): L = features.size(-1), K = queries.size(-1),
+ * E = distance_transform.size(-1)/2, n_freq = frequencies.size(0) (>= (E-1)/D/2).  L, K <= 128.
+ * weights / embeddings / factors (length) and neighbor_features (P, L) are fully written. */
+int dgs_aggregate_forward(int64_t P, int D, int L, int K, int E, int n_freq,
+                          const float* features, const float* transform, const float* queries, const float* keys,
+                          const float* frequencies, const float* distance_transform,
+                          const long long* indices, const long long* ranges, const float* dists,
+                          const float* densities, const float* inv_total,
+                          float* weights, float* embeddings, float* factors, float* neighbor_features, void* stream);
+/* AggregateNeighborsBackwardCUDA (aggregate_neighbors.cu:417-475); the six gradients are overwritten. */
+int dgs_aggregate_backward(int64_t P, int D, int L, int K, int E, int n_freq,
+                           const float* features, const float* transform, const float* queries, const float* keys,
+                           const float* frequencies, const float* distance_transform,
+                           const long long* indices, const long long* ranges, const float* dists,
+                           const float* densities, const float* weights, const float* embeddings,
+                           const float* factors, const float* inv_total, const float* dL_dneighbor_features,
+                           float* d_features, float* d_transform, float* d_queries, float* d_keys,
+                           float* d_frequencies, float* d_distance_transform, void* stream);
+
 /* Roofline denominators measured live (bench.py): which 0 = FP32 FFMA, 1 = MUFU.EX2.  Launches one
  * kernel on `stream`; *work_out = flop (FFMA counted as 2) resp. ex2 operations of that launch. */
 int dgs_microbench(int which, int iters, float* out_dev, double* work_out, void* stream);
