@@ -384,6 +384,12 @@ def main():
             hbm_peak, hbm_src = 6650.0, "fallback"
         T = D * (D + 1) // 2
         L = r["state"]["nr"]
+        try:   # dram bytes per launch from the committed ncu --set full capture (tools/ncu_summary.py)
+            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        except Exception:  # noqa: BLE001
+            tr = {}
+        traffic_note = f"ncu --set full capture profiles/{tr.get('_source', '?')} (cfg2, fn=gaussian)"
+        tr_ok = args.workload == "cfg2" and fn == 0
         pre_bytes = P * (4 * (D + T) + 8) + 12 * L + 24 * L + N * (4 * D + 12) + 24 * N
         line = {
             "metric": METRIC, "value": N * world * K / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
@@ -402,12 +408,17 @@ def main():
             "gpu_launches": int(r["launches"]),
             "clocks": r["clocks"],
             "roofline": {"kernel": "dgs_backward_kernel", "bound": "fp32", "achieved": ach_bwd, "peak": peaks["fp32_tflops"],
-                         "unit": "TFLOP/s", "frac": ach_bwd / peaks["fp32_tflops"], "traffic": None,
+                         "unit": "TFLOP/s", "frac": ach_bwd / peaks["fp32_tflops"],
+                         "traffic": tr.get("dgs_backward_kernel") if tr_ok else None,
+                         "traffic_source": traffic_note if tr_ok and tr else None,
+                         "algorithmic_bytes": N * (4 * D + 4 + 4 * C) + P * 4 * (D + C + T),
                          "peak_source": "FFMA microbenchmark (dgs_microbench) measured in this run, burst",
                          "flop_per_pair": f_bwd, "launch_ms": bwd_ms,
                          "sfu_frac": pairs / (bwd_ms * 1e-3) / 1e12 / peaks["ex2_tera_per_s"],
                          "forward": {"kernel": "dgs_forward_kernel", "achieved": ach_fwd, "frac": ach_fwd / peaks["fp32_tflops"],
                                      "flop_per_pair": f_fwd, "launch_ms": fwd_ms,
+                                     "traffic": tr.get("dgs_forward_kernel") if tr_ok else None,
+                                     "algorithmic_bytes": N * (4 * D + 4 + 4 * C),
                                      "sfu_frac": pairs / (fwd_ms * 1e-3) / 1e12 / peaks["ex2_tera_per_s"]},
                          "binning": {"bound": "hbm", "achieved": pre_bytes / (pre_ms * 1e-3) / 1e9, "peak": hbm_peak,
                                      "unit": "GB/s", "frac": pre_bytes / (pre_ms * 1e-3) / 1e9 / hbm_peak,

@@ -10,7 +10,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdgs_b200.so")
+LIB_PATH = os.environ.get("DGS_LIB_PATH") or os.path.join(_HERE, "libdgs_b200.so")   # DGS_LIB_PATH: tuning builds
 
 c_i32, c_u32, c_i64, c_u64, c_f32 = ctypes.c_int32, ctypes.c_uint32, ctypes.c_int64, ctypes.c_uint64, ctypes.c_float
 c_vp, c_sz = ctypes.c_void_p, ctypes.c_size_t
@@ -32,7 +32,7 @@ class Plan(ctypes.Structure):
         ("g_sort_tmp_off", c_u64),
         ("s_plan_off", c_u64), ("s_fine_start_off", c_u64), ("s_fine_ids_off", c_u64), ("s_fine_xyz_off", c_u64),
         ("s_fine_aabb_off", c_u64), ("s_coarse_aabb_off", c_u64), ("s_tmp_off", c_u64),
-        ("g_prec_off", c_u64), ("reserved", c_i32 * 6),
+        ("g_prec_off", c_u64), ("g_l1_mask_off", c_u64), ("mask_bytes", c_i32), ("reserved", c_i32 * 3),
     ]
 
     def as_dict(self):

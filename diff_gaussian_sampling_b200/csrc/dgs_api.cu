@@ -4,6 +4,7 @@
 // Nothing here allocates device memory or touches torch.
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include "dgs_common.cuh"
 #include "dgs_preprocess.cuh"
@@ -45,14 +46,16 @@ static PublicArrays public_arrays(void* buf, uint64_t L) {
 }
 
 struct GeomLayout {
-    size_t hdr, crec, touched, offsets, n1, n1_off, scan_tmp, total;
+    size_t hdr, crec, crecR, touched, offsets, n1, n1_off, scan_tmp, total;
 };
-static GeomLayout geom_layout(int64_t P) {
+static GeomLayout geom_layout(int64_t P, int D = 3) {
     GeomLayout g;
     const size_t p = (size_t)(P > 0 ? P : 1);
     size_t o = 0;
     g.hdr = o; o = dgs_a128(o + sizeof(DgsDevHeader));
-    g.crec = o; o = dgs_a128(o + p * sizeof(DgsCullRec));
+    (void)D;
+    g.crec = o; o = dgs_a128(o + p * 48);          // dgs_crec_bytes(3): the largest record
+    g.crecR = o; o = dgs_a128(o + p * 12);
     g.touched = o; o = dgs_a128(o + p * 4);
     g.offsets = o; o = dgs_a128(o + p * 4);
     g.n1 = o; o = dgs_a128(o + p * 4);
@@ -141,10 +144,12 @@ static void gauss_layout(dgs_plan_t* pl) {
     const size_t p = (size_t)(pl->P > 0 ? pl->P : 1);
     size_t o = dgs_public_bytes((uint64_t)pl->num_rendered);
     pl->g_plan_off = o; o = dgs_a128(o + sizeof(dgs_plan_t));
-    pl->g_crec_off = o; o = dgs_a128(o + p * sizeof(DgsCullRec));
+    pl->g_crec_off = o; o = dgs_a128(o + p * dgs_crec_bytes(pl->D));
     pl->g_l1_start_off = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     pl->g_l1_ids_off = o; o = dgs_a128(o + (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * 4);
     pl->g_prec_off = o; o = dgs_a128(o + p * (size_t)(pl->D == 3 ? 12 : 8) * 4);
+    pl->mask_bytes = pl->fine_per_coarse > 32 ? 8 : 4;
+    pl->g_l1_mask_off = o; o = dgs_a128(o + 4 * (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * (size_t)pl->mask_bytes);
     pl->g_sort_tmp_off = o; o += gauss_tmp_layout(pl).total;
     pl->binning_bytes = o + 128;
 }
@@ -155,11 +160,19 @@ static void gauss_layout(dgs_plan_t* pl) {
 static int choose_tiles(dgs_plan_t* pl) {
     const int D = pl->D;
     const double per_cell = (double)pl->N / (double)(pl->blocks > 0 ? pl->blocks : 1);
-    const double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 176.0);
+    double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 176.0);
+    if (const char* ev = getenv("DGS_TILE_TARGET")) {          // tuning knob (samples per fine tile)
+        const double v = atof(ev);
+        if (v >= 8.0) target = v;
+    }
     double f = pow(per_cell / target, 1.0 / D);
     int F = (int)floor(f);
     if (F < 1) F = 1;
-    const int fpc_default = D == 1 ? 8 : (D == 2 ? 4 : 2);
+    int fpc_default = D == 1 ? 8 : (D == 2 ? 4 : 2);
+    if (const char* ev = getenv("DGS_FPC")) {
+        const int v = atoi(ev);
+        if (v >= 1) fpc_default = v;
+    }
     int T1 = (F + fpc_default - 1) / fpc_default;
     // keep a Gaussian's tau-box from covering too many coarse tiles (list entries ~ P * prod(2R/w + 1))
     if (pl->mean_extent > 0.f) {
@@ -167,6 +180,10 @@ static int choose_tiles(dgs_plan_t* pl) {
         int cap = (int)floor(k / (double)pl->mean_extent);
         if (cap < 1) cap = 1;
         if (T1 > cap) T1 = cap;
+    }
+    if (const char* ev = getenv("DGS_T1")) {
+        const int v = atoi(ev);
+        if (v >= 1) T1 = v;
     }
     if (T1 < 1) T1 = 1;
     int fpc = (F + T1 - 1) / T1;
@@ -212,7 +229,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
         rc = dgs_launch_bounds(samples_dev, N, D, hdr, st);
         if (rc) return rc;
     }
-    rc = dgs_launch_crec(means_dev, conics_dev, P, D, plan->tau + DGS_TAU_MAX_EXTRA, hdr, (DgsCullRec*)(g + gl.crec), st);
+    rc = dgs_launch_crec(means_dev, conics_dev, P, D, plan->tau + DGS_TAU_MAX_EXTRA, hdr, (float4*)(g + gl.crec),
+                         (float*)(g + gl.crecR), st);
     if (rc) return rc;
     DgsDevHeader h;
     DGS_CUDA(cudaMemcpyAsync(&h, hdr, sizeof(h), cudaMemcpyDeviceToHost, st));
@@ -276,7 +294,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     uint32_t* n1 = (uint32_t*)(g + gl.n1);
     uint32_t* n1_off = (uint32_t*)(g + gl.n1_off);
     void* gscan = g + gl.scan_tmp;
-    const DgsCullRec* crec = (const DgsCullRec*)(g + gl.crec);
+    const float4* crec = (const float4*)(g + gl.crec);
+    const float* crecR = (const float*)(g + gl.crecR);
     const int64_t P = plan->P, N = plan->N;
     const int D = plan->D;
 
@@ -314,7 +333,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     if (rc) return rc;
 
     // --- size of the coarse-tile lists ---
-    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, plan, coarse_aabb, n1, nullptr, nullptr, nullptr, st);
+    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, n1, nullptr, nullptr, nullptr, st);
     if (rc) return rc;
     rc = dgs_exclusive_scan_u32(n1, n1_off, P, gscan, (uint32_t*)&hdr->n_l1, st);
     if (rc) return rc;
@@ -364,8 +383,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     if (rc) return rc;
 
     // internal: cull records move next to the lists; coarse-tile lists
-    DgsCullRec* crec = (DgsCullRec*)(gb + plan->g_crec_off);
-    if (P > 0) DGS_CUDA(cudaMemcpyAsync(crec, g + gl.crec, (size_t)P * sizeof(DgsCullRec), cudaMemcpyDeviceToDevice, st));
+    float4* crec = (float4*)(gb + plan->g_crec_off);
+    if (P > 0) DGS_CUDA(cudaMemcpyAsync(crec, g + gl.crec, (size_t)P * dgs_crec_bytes(plan->D), cudaMemcpyDeviceToDevice, st));
     uint32_t* l1_start = (uint32_t*)(gb + plan->g_l1_start_off);
     uint32_t* l1_ids = (uint32_t*)(gb + plan->g_l1_ids_off);
     uint32_t* keys_u = (uint32_t*)(tmp + tl.l1_keys_u);
@@ -373,7 +392,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     uint32_t* keys_s = (uint32_t*)(tmp + tl.l1_keys_s);
     const float* coarse_aabb = (const float*)(sb + plan->s_coarse_aabb_off);
     if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, plan, coarse_aabb, nullptr, n1_off, keys_u, vals_u, st);
+        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, nullptr, n1_off, keys_u, vals_u, st);
         if (rc) return rc;
         rc = dgs_sort_pairs_u32(keys_u, vals_u, keys_s, l1_ids, (uint32_t*)(tmp + tl.l1_alt_k), (uint32_t*)(tmp + tl.l1_alt_v),
                                 (int64_t)plan->n_l1, 0, ceil_log2((uint64_t)plan->n_coarse), tmp + tl.l1_sort_tmp, st);
@@ -381,6 +400,11 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     }
     rc = dgs_launch_l1_start(keys_s, (int64_t)plan->n_l1, plan->n_coarse, l1_start, st);
     if (rc) return rc;
+    if (plan->n_l1 > 0) {
+        rc = dgs_launch_l1_masks(plan, keys_s, l1_ids, crec, (const float*)(sb + plan->s_fine_aabb_off),
+                                 gb + plan->g_l1_mask_off, st);
+        if (rc) return rc;
+    }
     DGS_CUDA(cudaMemcpyAsync(gb + plan->g_plan_off, plan, sizeof(*plan), cudaMemcpyHostToDevice, st));
     DGS_CUDA(cudaMemcpyAsync(sb + plan->s_plan_off, plan, sizeof(*plan), cudaMemcpyHostToDevice, st));
     return 0;

@@ -22,23 +22,26 @@
 #include "dgs_field.cuh"
 #include "dgs_math.cuh"
 
+#ifndef BWD_MINB
+#define BWD_MINB 9
+#endif
 #define BWD_WARPS 4
 #define BWD_THREADS (BWD_WARPS * 32)
 #define BWD_QF 96    // fast-id queue slots per warp
 #define BWD_QG 64    // general-id queue slots per warp
+#define BWD_QRAW 96  // raw survivor-id queue slots per warp (< 32 left over + 64 new)
 #define BWD_EXACT_BIT 0x80000000u
 
 struct BwdArgs {
     const float* values; const float* conics; const float* dout;
     const float* prec;
-    const DgsCullRec* crec;
+    const void* mask; int mask64;                 // survivor bitmasks of this function level
     const uint32_t* l1_start; const uint32_t* l1_ids;
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
     const float* fine_aabb; const float* coarse_aabb;
     float* dmeans; float* dvalues; float* dconics;
     int64_t N;
     int C, ch0, fpcD;
-    float shrink, shrink2;
 };
 
 template <int D, int FN, int CB>
@@ -51,7 +54,7 @@ struct BwdCfg {
     static constexpr int SAMP_FLOATS = 256 * SW < 2048 ? 256 * SW : 2048;
     static constexpr int SCAP = SAMP_FLOATS / SW;           // samples per pass
     static constexpr int G = FN == 0 ? 2 : 1;               // Gaussians per lane on the fast path
-    static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG;
+    static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG + BWD_QRAW;
 };
 
 // per-pair VJP for FN >= 1: accumulates dV[c], dM[m], dC[k] (already multiplied by G)
@@ -261,7 +264,7 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
 }
 
 template <int D, int FN, int CB, bool VPOST>
-__global__ void __launch_bounds__(BWD_THREADS) dgs_backward_kernel(const BwdArgs A) {
+__global__ void __launch_bounds__(BWD_THREADS, BWD_MINB) dgs_backward_kernel(const BwdArgs A) {
     using K = BwdCfg<D, FN, CB>;
     constexpr int U = K::U, AFULL = K::AFULL, SW = K::SW, SW0 = K::SW0, SCAP = K::SCAP, NG = K::G;
     constexpr int PW = DGS_PREC_W(D);
@@ -272,6 +275,7 @@ __global__ void __launch_bounds__(BWD_THREADS) dgs_backward_kernel(const BwdArgs
     float* sS = smem + warp * K::WARP_WORDS;
     uint32_t* qF = (uint32_t*)(sS + K::SAMP_FLOATS);
     uint32_t* qG = qF + BWD_QF;
+    uint32_t* qR = qG + BWD_QG;
     const int64_t coarse = blockIdx.x;
     if (__float_as_int(A.coarse_aabb[coarse * 8 + 6]) == 0) return;
     const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
@@ -287,6 +291,7 @@ __global__ void __launch_bounds__(BWD_THREADS) dgs_backward_kernel(const BwdArgs
             const float4 b1 = *(const float4*)(A.fine_aabb + tile * 8 + 4);
             lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b0.w; hi[1] = b1.x; hi[2] = b1.y;
         }
+
         const uint32_t n = s1 - s0;
         const uint32_t n_pass = (n + SCAP - 1) / SCAP;
         const uint32_t per = (n + n_pass - 1) / n_pass;
@@ -317,65 +322,91 @@ __global__ void __launch_bounds__(BWD_THREADS) dgs_backward_kernel(const BwdArgs
             }
             __syncwarp();
 
-            int nf = 0, ng = 0;
-            for (uint32_t base = g0; base < g1; base += 32) {
-                const uint32_t e = base + lane;
-                bool pass = false, fast = false, exact = false;
-                uint32_t id = 0;
-                if (e < g1) {
-                    id = A.l1_ids[e];
-                    const DgsCullRec rec = A.crec[id];
-                    pass = dgs_cull_pass<D>(rec, lo, hi, A.shrink, A.shrink2);
+            int nf = 0, ng = 0, nq = 0;
+            for (uint32_t base = g0;; base += 64) {
+                // ---- survivors of this fine tile among the next 64 list entries -> raw id queue ----
+                if (base < g1) {
+                    const uint32_t e0 = base + lane, e1 = e0 + 32;
+                    uint32_t id0 = 0, id1 = 0;
+                    bool p0 = false, p1 = false;
+                    if (e0 < g1) { p0 = dgs_mask_bit(A.mask, A.mask64, e0, ft); id0 = A.l1_ids[e0]; }
+                    if (e1 < g1) { p1 = dgs_mask_bit(A.mask, A.mask64, e1, ft); id1 = A.l1_ids[e1]; }
+                    const uint32_t b0 = __ballot_sync(0xffffffffu, p0), b1 = __ballot_sync(0xffffffffu, p1);
+                    if (p0) qR[nq + __popc(b0 & lt)] = id0;
+                    nq += __popc(b0);
+                    if (p1) qR[nq + __popc(b1 & lt)] = id1;
+                    nq += __popc(b1);
                 }
-                if (pass) {
-                    const float* pr = A.prec + (int64_t)id * PW;
-                    fast = (__float_as_uint(__ldg(pr + PW - 1)) & DGS_PREC_FAST) != 0u;
+                const bool end = base + 64 >= g1;
+                __syncwarp();
+                // ---- classify 32 queued Gaussians at a time into the fast / general queues ----
+                while (nq >= 32 || (end && nq > 0)) {
+                    const int cnt = nq < 32 ? nq : 32;
+                    const bool pass = lane < cnt;
+                    const bool last = end && nq <= 32;
+                    bool fast = false, exact = false;
+                    uint32_t id = 0;
+                    if (pass) {
+                        id = qR[lane];
+                        const float4* p4 = (const float4*)(A.prec + (int64_t)id * PW);
+                        const float4 v0 = __ldg(p4);
+                        const float4 vl = __ldg(p4 + PW / 4 - 1);
+                        const float m3[3] = {v0.x, v0.y, v0.z};
+                        fast = (__float_as_uint(vl.w) & DGS_PREC_FAST) != 0u;
 #pragma unroll
-                    for (int d = 0; d < D; d++) {
-                        const float m = __ldg(pr + d);
-                        const float xmin = m - hi[d], xmax = m - lo[d];
-                        if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;
-                        if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;
+                        for (int d = 0; d < D; d++) {
+                            const float xmin = m3[d] - hi[d], xmax = m3[d] - lo[d];
+                            if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;
+                            if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;
+                        }
                     }
-                }
-                const uint32_t balP = __ballot_sync(0xffffffffu, pass);
-                const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
-                const uint32_t balG = balP & ~balF;
-                if (pass) {
-                    if (fast) qF[nf + __popc(balF & lt)] = id;
-                    else qG[ng + __popc(balG & lt)] = id | (exact ? BWD_EXACT_BIT : 0u);
-                }
-                nf += __popc(balF);
-                ng += __popc(balG);
-                const bool last = base + 32 >= g1;
-                __syncwarp();
-                if (nf >= 32 * NG) {
-                    bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane);
-                    const int rem = nf - 32 * NG;          // < 32
-                    uint32_t keep = 0;
-                    if (lane < rem) keep = qF[32 * NG + lane];
+                    const uint32_t balP = __ballot_sync(0xffffffffu, pass);
+                    const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
+                    const uint32_t balG = balP & ~balF;
+                    if (pass) {
+                        if (fast) qF[nf + __popc(balF & lt)] = id;
+                        else qG[ng + __popc(balG & lt)] = id | (exact ? BWD_EXACT_BIT : 0u);
+                    }
+                    nf += __popc(balF);
+                    ng += __popc(balG);
+                    const int remq = nq - cnt;
+                    uint32_t keep = 0, keep2 = 0;
+                    if (lane < remq) keep = qR[32 + lane];
+                    if (lane + 32 < remq) keep2 = qR[64 + lane];
                     __syncwarp();
-                    if (lane < rem) qF[lane] = keep;
-                    nf = rem;
+                    if (lane < remq) qR[lane] = keep;
+                    if (lane + 32 < remq) qR[32 + lane] = keep2;
+                    nq = remq;
+                    __syncwarp();
+                    if (nf >= 32 * NG) {
+                        bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane);
+                        const int rem = nf - 32 * NG;          // < 32
+                        uint32_t kp = 0;
+                        if (lane < rem) kp = qF[32 * NG + lane];
+                        __syncwarp();
+                        if (lane < rem) qF[lane] = kp;
+                        nf = rem;
+                        __syncwarp();
+                    }
+                    if (last && nf > 0) {
+                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane);
+                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane);
+                        nf = 0;
+                    }
+                    while (ng >= 32 || (last && ng > 0)) {
+                        const int c2 = ng < 32 ? ng : 32;
+                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, c2, lane);
+                        const int rem = ng - c2;          // < 32
+                        uint32_t kp = 0;
+                        if (lane < rem) kp = qG[32 + lane];
+                        __syncwarp();
+                        if (lane < rem) qG[lane] = kp;
+                        ng = rem;
+                        __syncwarp();
+                    }
                     __syncwarp();
                 }
-                if (last && nf > 0) {
-                    if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane);
-                    else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane);
-                    nf = 0;
-                }
-                while (ng >= 32 || (last && ng > 0)) {
-                    const int cnt = ng < 32 ? ng : 32;
-                    bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, cnt, lane);
-                    const int rem = ng - cnt;          // < 32
-                    uint32_t keep = 0;
-                    if (lane < rem) keep = qG[32 + lane];
-                    __syncwarp();
-                    if (lane < rem) qG[lane] = keep;
-                    ng = rem;
-                    __syncwarp();
-                }
-                __syncwarp();
+                if (end) break;
             }
         }
     }
@@ -447,7 +478,8 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     BwdArgs a;
     a.values = values; a.conics = conics; a.dout = dout;
     a.prec = (const float*)(gbuf + plan->g_prec_off);
-    a.crec = (const DgsCullRec*)(gbuf + plan->g_crec_off);
+    a.mask64 = plan->mask_bytes == 8 ? 1 : 0;
+    a.mask = gbuf + plan->g_l1_mask_off + (size_t)(fn < 0 ? 0 : (fn > 3 ? 3 : fn)) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
     a.fine_start = (const uint32_t*)(sbuf + plan->s_fine_start_off);
@@ -457,10 +489,6 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
     a.dmeans = dmeans; a.dvalues = dvalues; a.dconics = dconics;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
-    const float tau_max = plan->tau + DGS_TAU_MAX_EXTRA;
-    const float ratio = dgs_tau_for(plan, fn) / tau_max;
-    a.shrink2 = ratio < 1.f ? ratio * 1.00002f : 1.f;
-    a.shrink = ratio < 1.f ? sqrtf(ratio) * 1.00001f : 1.f;
     const int T = plan->D * (plan->D + 1) / 2;
     // the kernels accumulate: start from zero whatever the caller left in the buffers
     DGS_CUDA(cudaMemsetAsync(dmeans, 0, (size_t)plan->P * plan->D * 4, st));

@@ -37,17 +37,17 @@ void dgs_set_error(const char* fmt, ...);
 static inline size_t dgs_a128(size_t x) { return (x + 127) & ~(size_t)127; }
 static inline int dgs_cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
-// --- per-Gaussian cull record (32 B) -------------------------------------------------
-// mu: mean at preprocess time; R: half width of the box around the ellipsoid
-// power >= -tau_max along each axis; rs2: squared radius of the sphere around it;
-// flags bit0: never cull (far from the sample box, or conic not positive definite).
-struct __align__(16) DgsCullRec {
-    float mu[3];
-    float R[3];
-    float rs2;
-    uint32_t flags;
-};
-#define DGS_CREC_ALWAYS 1u
+// --- per-Gaussian cull record ----------------------------------------------------------
+// Built at preprocess time from the means / conics the accumulation kernels evaluate.  Stored as
+// float4s (stride DGS_CREC_V4(D)):
+//   D <= 2 (32 B): {mu0, mu1, R0, R1} {rs2, C0, C1, C2}
+//   D == 3 (48 B): {mu0, mu1, mu2, rs2} {C0, C1, C2, C3} {C4, C5, 0, 0}
+// R: half width of the box around the ellipsoid power >= -tau_max along each axis; rs2: squared radius
+// of the sphere around it (rs2 < 0: never cull — far from the sample box, or conic not positive
+// definite); C: the packed conic for the ellipsoid test, all zero (test always passes) when the
+// ellipsoid is too large for the nearest-image argument (some R_d >= 0.45).
+#define DGS_CREC_V4(D) ((D) == 3 ? 3 : 2)
+static inline size_t dgs_crec_bytes(int D) { return (size_t)DGS_CREC_V4(D) * 16; }
 
 // --- device-side header written by the step-1/2 kernels and copied back to the host ---
 struct DgsDevHeader {

@@ -22,15 +22,19 @@
 #include "dgs_field.cuh"
 #include "dgs_math.cuh"
 
+#ifndef FWD_MINB
+#define FWD_MINB 5
+#endif
 #define FWD_WARPS 4
 #define FWD_THREADS (FWD_WARPS * 32)
 #define FWD_CAPF 64   // staged fast records per warp (flushed when more than CAPF-32 are waiting)
 #define FWD_CAPG 32   // staged general records per warp
+#define FWD_QRAW 96   // queued survivor ids per warp (< 32 left over + 64 new)
 
 struct FwdArgs {
     const float* values; const float* conics;
     const float* prec;
-    const DgsCullRec* crec;
+    const void* mask; int mask64;                 // survivor bitmasks of this function level
     const uint32_t* l1_start; const uint32_t* l1_ids;
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
     const float* fine_aabb; const float* coarse_aabb;
@@ -38,7 +42,6 @@ struct FwdArgs {
     unsigned long long* pair_counter;
     int64_t N;
     int C, ch0, fpcD;
-    float shrink, shrink2;
 };
 
 template <int D, int FN, int CB>
@@ -134,16 +137,18 @@ __device__ __forceinline__ void fwd_eval_general(const float* __restrict__ sG, i
 }
 
 template <int D, int FN, int CB, bool COUNT_ONLY>
-__global__ void __launch_bounds__(FWD_THREADS) dgs_forward_kernel(const FwdArgs A) {
+__global__ void __launch_bounds__(FWD_THREADS, FWD_MINB) dgs_forward_kernel(const FwdArgs A) {
     using K = FwdCfg<D, FN, CB>;
     constexpr int T = K::T, U = K::U, AFULL = K::AFULL, SMAX = K::SMAX, FW = K::FW, GW = K::GW, GW0 = K::GW0;
     constexpr int PW = DGS_PREC_W(D);
     __shared__ __align__(16) float smem[COUNT_ONLY ? 4 : FWD_WARPS * K::WARP_FLOATS];
+    __shared__ uint32_t s_qraw[COUNT_ONLY ? 1 : FWD_WARPS * FWD_QRAW];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     float* sF = smem + (COUNT_ONLY ? 0 : warp * K::WARP_FLOATS);
     float* sG = sF + (COUNT_ONLY ? 0 : FWD_CAPF * FW);
+    uint32_t* qR = s_qraw + (COUNT_ONLY ? 0 : warp * FWD_QRAW);
     const int64_t coarse = blockIdx.x;
     if (__float_as_int(A.coarse_aabb[coarse * 8 + 6]) == 0) return;   // no samples here
     const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
@@ -159,6 +164,7 @@ __global__ void __launch_bounds__(FWD_THREADS) dgs_forward_kernel(const FwdArgs 
             const float4 b1 = *(const float4*)(A.fine_aabb + tile * 8 + 4);
             lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b0.w; hi[1] = b1.x; hi[2] = b1.y;
         }
+
         // balanced passes of at most 32*SMAX samples
         const uint32_t n = s1 - s0;
         const uint32_t n_pass = (n + 32 * SMAX - 1) / (32 * SMAX);
@@ -180,84 +186,111 @@ __global__ void __launch_bounds__(FWD_THREADS) dgs_forward_kernel(const FwdArgs 
                     for (int c = 0; c < CB; c++) acc[i][u][c] = 0.f;
             }
 
-            int nf = 0, ng = 0;
-            for (uint32_t base = g0; base < g1; base += 32) {
-                const uint32_t e = base + lane;
-                bool pass = false, fast = false, exact = false;
-                uint32_t id = 0;
-                float pr[PW];
-                if (e < g1) {
-                    id = A.l1_ids[e];
-                    const DgsCullRec rec = A.crec[id];
-                    pass = dgs_cull_pass<D>(rec, lo, hi, A.shrink, A.shrink2);
-                }
-                if (pass && !COUNT_ONLY) {
-                    const float4* p4 = (const float4*)(A.prec + (int64_t)id * PW);
-#pragma unroll
-                    for (int q = 0; q < PW / 4; q++) {
-                        const float4 v = __ldg(p4 + q);
-                        pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
-                    }
-                    fast = (__float_as_uint(pr[PW - 1]) & DGS_PREC_FAST) != 0u;
-#pragma unroll
-                    for (int d = 0; d < D; d++) {
-                        // fp32 subtraction is monotone: every sample of the tile has fl(mu - x) in [xmin, xmax]
-                        const float xmin = pr[d] - hi[d], xmax = pr[d] - lo[d];
-                        if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;            // some sample wraps (forward.cu:150)
-                        if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;  // fmod arm differs from -/+ 2
-                    }
-                }
-                const uint32_t balP = __ballot_sync(0xffffffffu, pass);
-                if (COUNT_ONLY) {
-                    pairs += (unsigned long long)__popc(balP) * (pe - pb);
-                    continue;
-                }
-                const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
-                const uint32_t balG = balP & ~balF;
-                if (pass) {
-                    if (fast) {
-                        float* r = sF + (nf + __popc(balF & lt)) * FW;
-#pragma unroll
-                        for (int q = 0; q < D + T; q++) r[q] = pr[q];
-                        if (FN > 0) {
-#pragma unroll
-                            for (int k = 0; k < T; k++) r[D + T + k] = A.conics[(int64_t)id * T + k];
-                        }
-#pragma unroll
-                        for (int c = 0; c < CB; c++) r[D + T + (FN > 0 ? T : 0) + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
+            int nf = 0, ng = 0, nq = 0;
+            for (uint32_t base = g0;; base += 64) {
+                // ---- survivors of this fine tile among the next 64 list entries -> raw id queue ----
+                if (base < g1) {
+                    const uint32_t e0 = base + lane, e1 = e0 + 32;
+                    uint32_t id0 = 0, id1 = 0;
+                    bool p0 = false, p1 = false;
+                    if (e0 < g1) { p0 = dgs_mask_bit(A.mask, A.mask64, e0, ft); if (!COUNT_ONLY) id0 = A.l1_ids[e0]; }
+                    if (e1 < g1) { p1 = dgs_mask_bit(A.mask, A.mask64, e1, ft); if (!COUNT_ONLY) id1 = A.l1_ids[e1]; }
+                    const uint32_t b0 = __ballot_sync(0xffffffffu, p0), b1 = __ballot_sync(0xffffffffu, p1);
+                    if (COUNT_ONLY) {
+                        pairs += (unsigned long long)(__popc(b0) + __popc(b1)) * (pe - pb);
                     } else {
-                        float* r = sG + (ng + __popc(balG & lt)) * GW;
-#pragma unroll
-                        for (int d = 0; d < D; d++) r[d] = pr[d];
-#pragma unroll
-                        for (int k = 0; k < T; k++) r[D + k] = A.conics[(int64_t)id * T + k];
-#pragma unroll
-                        for (int c = 0; c < CB; c++) r[D + T + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
-                        r[GW0 - 1] = exact ? 1.f : 0.f;
+                        if (p0) qR[nq + __popc(b0 & lt)] = id0;
+                        nq += __popc(b0);
+                        if (p1) qR[nq + __popc(b1 & lt)] = id1;
+                        nq += __popc(b1);
                     }
                 }
-                nf += __popc(balF);
-                ng += __popc(balG);
-                const bool last = base + 32 >= g1;
+                const bool end = base + 64 >= g1;
+                if (COUNT_ONLY) { if (end) break; continue; }
                 __syncwarp();
-                if (nf > FWD_CAPF - 32 || (last && nf > 0)) {
-                    switch (s_eff) {
-                        case 1: fwd_eval_fast<D, FN, CB, 1>(sF, nf, x, acc); break;
-                        case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1>(sF, nf, x, acc); break;
-                        case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1>(sF, nf, x, acc); break;
-                        case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1>(sF, nf, x, acc); break;
-                        case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1>(sF, nf, x, acc); break;
-                        case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1>(sF, nf, x, acc); break;
-                        case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1>(sF, nf, x, acc); break;
-                        default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1>(sF, nf, x, acc); break;
+                // ---- drain: 32 queued Gaussians at a time, every lane gathers and stages one record ----
+                while (nq >= 32 || (end && nq > 0)) {
+                    const int cnt = nq < 32 ? nq : 32;
+                    const bool pass = lane < cnt;
+                    const bool last = end && nq <= 32;
+                    bool fast = false, exact = false;
+                    uint32_t id = 0;
+                    float pr[PW];
+                    if (pass) {
+                        id = qR[lane];
+                        const float4* p4 = (const float4*)(A.prec + (int64_t)id * PW);
+#pragma unroll
+                        for (int q = 0; q < PW / 4; q++) {
+                            const float4 v = __ldg(p4 + q);
+                            pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
+                        }
+                        fast = (__float_as_uint(pr[PW - 1]) & DGS_PREC_FAST) != 0u;
+#pragma unroll
+                        for (int d = 0; d < D; d++) {
+                            // fp32 subtraction is monotone: every sample of the tile has fl(mu - x) in [xmin, xmax]
+                            const float xmin = pr[d] - hi[d], xmax = pr[d] - lo[d];
+                            if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;            // some sample wraps (forward.cu:150)
+                            if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;  // fmod arm differs from -/+ 2
+                        }
                     }
-                    nf = 0;
+                    const uint32_t balP = __ballot_sync(0xffffffffu, pass);
+                    const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
+                    const uint32_t balG = balP & ~balF;
+                    if (pass) {
+                        if (fast) {
+                            float* r = sF + (nf + __popc(balF & lt)) * FW;
+#pragma unroll
+                            for (int q = 0; q < D + T; q++) r[q] = pr[q];
+                            if (FN > 0) {
+#pragma unroll
+                                for (int k = 0; k < T; k++) r[D + T + k] = A.conics[(int64_t)id * T + k];
+                            }
+#pragma unroll
+                            for (int c = 0; c < CB; c++) r[D + T + (FN > 0 ? T : 0) + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
+                        } else {
+                            float* r = sG + (ng + __popc(balG & lt)) * GW;
+#pragma unroll
+                            for (int d = 0; d < D; d++) r[d] = pr[d];
+#pragma unroll
+                            for (int k = 0; k < T; k++) r[D + k] = A.conics[(int64_t)id * T + k];
+#pragma unroll
+                            for (int c = 0; c < CB; c++) r[D + T + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
+                            r[GW0 - 1] = exact ? 1.f : 0.f;
+                        }
+                    }
+                    nf += __popc(balF);
+                    ng += __popc(balG);
+                    // move the rest of the queue to the front
+                    const int rem = nq - cnt;
+                    uint32_t keep = 0;
+                    if (lane < rem) keep = qR[32 + lane];
+                    uint32_t keep2 = 0;
+                    if (lane + 32 < rem) keep2 = qR[64 + lane];
+                    __syncwarp();
+                    if (lane < rem) qR[lane] = keep;
+                    if (lane + 32 < rem) qR[32 + lane] = keep2;
+                    nq = rem;
+                    __syncwarp();
+                    if (nf > FWD_CAPF - 32 || (last && nf > 0)) {
+                        switch (s_eff) {
+                            case 1: fwd_eval_fast<D, FN, CB, 1>(sF, nf, x, acc); break;
+                            case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1>(sF, nf, x, acc); break;
+                            case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1>(sF, nf, x, acc); break;
+                            case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1>(sF, nf, x, acc); break;
+                            case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1>(sF, nf, x, acc); break;
+                            case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1>(sF, nf, x, acc); break;
+                            case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1>(sF, nf, x, acc); break;
+                            default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1>(sF, nf, x, acc); break;
+                        }
+                        nf = 0;
+                    }
+                    if (ng > FWD_CAPG - 32 || (last && ng > 0)) {
+                        fwd_eval_general<D, FN, CB>(sG, ng, s_eff, x, acc);
+                        ng = 0;
+                    }
+                    __syncwarp();
                 }
-                if (ng > FWD_CAPG - 32 || (last && ng > 0)) {
-                    fwd_eval_general<D, FN, CB>(sG, ng, s_eff, x, acc);
-                    ng = 0;
-                }
-                __syncwarp();
+                if (end) break;
             }
             if (!COUNT_ONLY) {
 #pragma unroll
@@ -316,7 +349,8 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     FwdArgs a;
     a.values = values; a.conics = conics;
     a.prec = (const float*)(gbuf + plan->g_prec_off);
-    a.crec = (const DgsCullRec*)(gbuf + plan->g_crec_off);
+    a.mask64 = plan->mask_bytes == 8 ? 1 : 0;
+    a.mask = gbuf + plan->g_l1_mask_off + (size_t)(fn < 0 ? 0 : (fn > 3 ? 3 : fn)) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
     a.fine_start = (const uint32_t*)(sbuf + plan->s_fine_start_off);
@@ -326,10 +360,6 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
     a.out = out; a.pair_counter = pair_counter;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
-    const float tau_max = plan->tau + DGS_TAU_MAX_EXTRA;
-    const float ratio = dgs_tau_for(plan, fn) / tau_max;
-    a.shrink2 = ratio < 1.f ? ratio * 1.00002f : 1.f;
-    a.shrink = ratio < 1.f ? sqrtf(ratio) * 1.00001f : 1.f;
     if (pair_counter) {
         DGS_NOTE_LAUNCHES(1);
         if (plan->D == 1) dgs_forward_kernel<1, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);

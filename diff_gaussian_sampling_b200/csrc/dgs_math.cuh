@@ -117,18 +117,114 @@ __device__ __forceinline__ float dgs_axis_dist(float m, float lo, float hi) {
     return fminf(d0, fminf(dm, dp));
 }
 
-// conservative test: can any point of the box [lo,hi] have power >= -tau for this Gaussian?
-// `shrink` (<= 1) scales the record's tau_max extents down to the tau of the function at hand.
-template <int D>
-__device__ __forceinline__ bool dgs_cull_pass(const DgsCullRec& r, const float* lo, const float* hi, float shrink, float shrink2) {
-    if (r.flags & DGS_CREC_ALWAYS) return true;
-    float d2 = 0.f;
-    bool ok = true;
+// Box of the samples of one tile, with its centre and half widths.
+struct DgsTileBox {
+    float lo[3], hi[3], ctr[3], half[3];
+    __device__ __forceinline__ void set(const float* l, const float* h) {
 #pragma unroll
-    for (int d = 0; d < D; d++) {
-        const float dist = dgs_axis_dist(r.mu[d], lo[d], hi[d]);
-        ok = ok && (dist <= r.R[d] * shrink);
-        d2 = fmaf(dist, dist, d2);
+        for (int d = 0; d < 3; d++) {
+            lo[d] = l[d]; hi[d] = h[d];
+            ctr[d] = 0.5f * (l[d] + h[d]);
+            half[d] = fmaxf(h[d] - ctr[d], ctr[d] - l[d]);   // >= the exact half width after rounding of ctr
+        }
     }
-    return ok && (d2 <= r.rs2 * shrink2);
+};
+
+struct DgsCullRecView {
+    float mu[3], R[3], rs2, C[6];
+};
+template <int D>
+__device__ __forceinline__ DgsCullRecView dgs_crec_load(const float4* __restrict__ crec, int64_t id) {
+    DgsCullRecView r;
+    const float4 a = __ldg(crec + id * DGS_CREC_V4(D));
+    const float4 b = __ldg(crec + id * DGS_CREC_V4(D) + 1);
+    if (D == 3) {
+        const float4 c = __ldg(crec + id * DGS_CREC_V4(D) + 2);
+        r.mu[0] = a.x; r.mu[1] = a.y; r.mu[2] = a.z; r.rs2 = a.w;
+        r.C[0] = b.x; r.C[1] = b.y; r.C[2] = b.z; r.C[3] = b.w; r.C[4] = c.x; r.C[5] = c.y;
+        r.R[0] = r.R[1] = r.R[2] = INFINITY;
+    } else {
+        r.mu[0] = a.x; r.mu[1] = a.y; r.mu[2] = 0.f; r.R[0] = a.z; r.R[1] = a.w; r.R[2] = INFINITY;
+        r.rs2 = b.x; r.C[0] = b.y; r.C[1] = b.z; r.C[2] = b.w; r.C[3] = r.C[4] = r.C[5] = 0.f;
+    }
+    return r;
+}
+
+// Conservative test: can any point of the box have power >= -tau for this Gaussian?  Three sound
+// necessary conditions, all evaluated on period-2 images of the mean:
+//   (1) D <= 2: per-axis distance to the box <= R_d (bounding box of the tau_max ellipsoid),
+//   (2) squared distance to the box <= rs2 (bounding sphere),
+//   (3) ellipsoid: sqrt(X^T C X) <= sqrt(2 tau) + max_corner sqrt(h^T C h), X = box centre - nearest
+//       image of the mean (triangle inequality in the metric of C; C is zeroed, i.e. the test always
+//       passes, unless every R_d < 0.45, which makes the image that passes (1)/(2) the nearest one:
+//       tile boxes are at most one 0.51 cell wide).
+// `shrink`/`shrink2` (<= 1) scale the record's tau_max extents down to the tau of the function at
+// hand; two_tau = 2 * that tau.
+// The geometry of one (Gaussian, box) test, independent of tau: per-axis and squared distance from the
+// nearest period-2 image of the mean to the box, q = X^T C X at the box centre, h2 = max_corner h^T C h.
+// Choosing, per axis, the image nearest to the box centre minimises the distance to the (symmetric) box,
+// i.e. equals the minimum over all images.
+template <int D>
+struct DgsCullGeom {
+    float dist[D], d2, q, h2, sq;
+    __device__ __forceinline__ void measure(const DgsCullRecView& r, const DgsTileBox& b) {
+        float X[D];
+        d2 = 0.f;
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            float x = b.ctr[d] - r.mu[d];
+            x = x > 1.0f ? x - 2.0f : (x < -1.0f ? x + 2.0f : x);
+            X[d] = x;
+            // 1e-6 relative slack covers the rounding of ctr and of the subtraction
+            dist[d] = fmaxf(0.f, fabsf(x) * 0.999999f - b.half[d]);
+            d2 = fmaf(dist[d], dist[d], d2);
+        }
+        if (D == 1) {
+            q = r.C[0] * X[0] * X[0];
+            h2 = r.C[0] * b.half[0] * b.half[0];
+        } else if (D == 2) {
+            q = fmaf(r.C[0] * X[0], X[0], fmaf(r.C[2] * X[1], X[1], 2.0f * r.C[1] * X[0] * X[1]));
+            h2 = fmaf(r.C[0] * b.half[0], b.half[0], fmaf(r.C[2] * b.half[1], b.half[1], 2.0f * fabsf(r.C[1]) * b.half[0] * b.half[1]));
+        } else {
+            q = r.C[0] * X[0] * X[0] + r.C[3] * X[1] * X[1] + r.C[5] * X[2] * X[2]
+                + 2.0f * (r.C[1] * X[0] * X[1] + r.C[2] * X[0] * X[2] + r.C[4] * X[1] * X[2]);
+            const float* h = b.half;
+            h2 = r.C[0] * h[0] * h[0] + r.C[3] * h[1] * h[1] + r.C[5] * h[2] * h[2]
+                 + 2.0f * (fabsf(r.C[1]) * h[0] * h[1] + fabsf(r.C[2]) * h[0] * h[2] + fabsf(r.C[4]) * h[1] * h[2]);
+        }
+        sq = sqrtf(fmaxf(h2, 0.f));
+    }
+    // shrink/shrink2 scale the record's tau_max extents to the tau at hand; two_tau = 2 tau, s2t = sqrt(2 tau)
+    __device__ __forceinline__ bool decide(const DgsCullRecView& r, float shrink, float shrink2, float two_tau, float s2t) const {
+        bool ok = d2 <= r.rs2 * shrink2;
+        if (D < 3) {
+#pragma unroll
+            for (int d = 0; d < D; d++) ok = ok && (dist[d] <= r.R[d] * shrink);
+        }
+        const float rhs = two_tau + h2 + 2.0f * s2t * sq;
+        return ok && (q <= fmaf(rhs, 1.001f, 1e-5f));
+    }
+};
+
+// Conservative test: can any point of the box have power >= -tau for this Gaussian?  Three sound
+// necessary conditions on the nearest period-2 image of the mean:
+//   (1) D <= 2: per-axis distance to the box <= R_d (bounding box of the tau_max ellipsoid),
+//   (2) squared distance to the box <= rs2 (bounding sphere),
+//   (3) ellipsoid: sqrt(X^T C X) <= sqrt(2 tau) + max_corner sqrt(h^T C h), X = box centre - image
+//       (triangle inequality in the metric of C; C is zeroed, i.e. the test always passes, unless
+//       every R_d < 0.45, which makes the image that can pass (1)/(2) the nearest one: tile boxes
+//       are at most one 0.51 cell wide).
+template <int D>
+__device__ __forceinline__ bool dgs_cull_pass(const DgsCullRecView& r, const DgsTileBox& b, float shrink, float shrink2,
+                                              float two_tau) {
+    if (r.rs2 < 0.f) return true;
+    DgsCullGeom<D> g;
+    g.measure(r, b);
+    return g.decide(r, shrink, shrink2, two_tau, sqrtf(two_tau));
+}
+
+// bit `ft` of the survivor mask of coarse-list entry e (masks are u32 or u64, see dgs_l1_mask_kernel)
+__device__ __forceinline__ bool dgs_mask_bit(const void* __restrict__ mask, int mask64, uint32_t e, int ft) {
+    if (mask64) return (__ldg((const unsigned long long*)mask + e) >> ft) & 1ull;
+    return (__ldg((const uint32_t*)mask + e) >> ft) & 1u;
 }

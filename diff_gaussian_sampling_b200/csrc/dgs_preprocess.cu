@@ -86,14 +86,14 @@ int dgs_launch_header_init(DgsDevHeader* h, cudaStream_t st) {
 template <int D>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __restrict__ means, const float* __restrict__ conics,
                                                                int64_t P, float tau_max, DgsDevHeader* __restrict__ h,
-                                                               DgsCullRec* __restrict__ crec) {
+                                                               float4* __restrict__ crec, float* __restrict__ crecR) {
     constexpr int T = D * (D + 1) / 2;
     const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
     double ext = 0.0;
     unsigned cnt = 0;
     uint32_t hflags = 0;
     if (i < P) {
-        DgsCullRec r;
+        float r_mu[3], r_R[3], r_rs2;
         float con[T];
 #pragma unroll
         for (int k = 0; k < T; k++) con[k] = conics[i * T + k];
@@ -133,18 +133,17 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
             double dummy;
             lmax = dgs_lambda_max3(sig, &dummy) * (1.0 + 1e-5);
         }
-        uint32_t flags = 0;
         bool finite = pd && isfinite(lmax) && lmax > 0.0;
 #pragma unroll
         for (int d = 0; d < D; d++) finite = finite && isfinite(var[d]) && var[d] > 0.0;
 #pragma unroll
-        for (int d = 0; d < 3; d++) { r.mu[d] = 0.f; r.R[d] = 0.f; }
-        r.rs2 = 0.f;
+        for (int d = 0; d < 3; d++) { r_mu[d] = 0.f; r_R[d] = 0.f; }
+        r_rs2 = -1.f;
         bool far = false;
 #pragma unroll
         for (int d = 0; d < D; d++) {
             const float m = means[i * D + d];
-            r.mu[d] = m;
+            r_mu[d] = m;
             // fp32 subtraction is monotone, so |fl(m - x)| <= max(|fl(m - lo)|, |fl(m - hi)|) for every
             // sample x in [lo, hi]: exactly the pairs for which the fmod arm of forward.cu:150-156
             // differs from X -/+ 2
@@ -152,21 +151,34 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
             if (!(reach < 2.0f)) far = true;
         }
         if (far) hflags |= DGS_HDR_EXACT_WRAP;
-        if (!finite || far) {
-            flags |= DGS_CREC_ALWAYS;
-        } else {
+        bool small = true;
+        if (finite && !far) {
 #pragma unroll
             for (int d = 0; d < D; d++) {
                 const float R = (float)sqrt(2.0 * (double)tau_max * var[d]) * 1.0001f + 1e-6f;
-                r.R[d] = R;
+                r_R[d] = R;
+                small = small && (R < 0.45f);
                 ext += R;
                 cnt++;
             }
             const float rs = (float)sqrt(2.0 * (double)tau_max * lmax) * 1.0001f + 1e-6f;
-            r.rs2 = rs * rs;
+            r_rs2 = rs * rs;
         }
-        r.flags = flags;
-        crec[i] = r;
+        float C[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (finite && !far && small) {
+#pragma unroll
+            for (int k = 0; k < T; k++) C[k] = con[k];
+        }
+        if (D == 3) {
+            crec[i * 3] = make_float4(r_mu[0], r_mu[1], r_mu[2], r_rs2);
+            crec[i * 3 + 1] = make_float4(C[0], C[1], C[2], C[3]);
+            crec[i * 3 + 2] = make_float4(C[4], C[5], 0.f, 0.f);
+        } else {
+            crec[i * 2] = make_float4(r_mu[0], r_mu[1], r_R[0], r_R[1]);
+            crec[i * 2 + 1] = make_float4(r_rs2, C[0], C[1], C[2]);
+        }
+#pragma unroll
+        for (int d = 0; d < 3; d++) crecR[i * 3 + d] = r_R[d];
     }
     // block reduction of the statistics
     __shared__ double s_ext[DGS_THREADS / 32];
@@ -191,12 +203,12 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
 }
 
 int dgs_launch_crec(const float* means, const float* conics, int64_t P, int D, float tau_max, DgsDevHeader* h,
-                    DgsCullRec* crec, cudaStream_t st) {
+                    float4* crec, float* crecR, cudaStream_t st) {
     if (P <= 0) return 0;
     const int nb = dgs_cdiv(P, DGS_THREADS);
-    if (D == 1) dgs_crec_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
-    else if (D == 2) dgs_crec_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
-    else dgs_crec_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec);
+    if (D == 1) dgs_crec_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec, crecR);
+    else if (D == 2) dgs_crec_kernel<2><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec, crecR);
+    else dgs_crec_kernel<3><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, tau_max, h, crec, crecR);
     DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
@@ -533,7 +545,8 @@ int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const ui
 // bounding box of the samples actually in the tile.
 template <int D, bool EMIT>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __restrict__ means, const float* __restrict__ radii,
-                                                             const DgsCullRec* __restrict__ crec, int64_t P, DgsGrid G, int cpc,
+                                                             const float4* __restrict__ crec, const float* __restrict__ crecR,
+                                                             float two_tau, int64_t P, DgsGrid G, int cpc,
                                                              int T1, int blocks,
                                                              const float* __restrict__ coarse_aabb, uint32_t* __restrict__ n1,
                                                              const uint32_t* __restrict__ n1_off, uint32_t* __restrict__ keys,
@@ -546,14 +559,18 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         float p[D];
 #pragma unroll
         for (int k = 0; k < D; k++) p[k] = means[i * D + k];
-        const DgsCullRec rec = crec[i];
+        const DgsCullRecView rec = dgs_crec_load<D>(crec, i);
+        const float recR[3] = {crecR[i * 3], crecR[i * 3 + 1], crecR[i * 3 + 2]};
+        const bool always = rec.rs2 < 0.f;
         uint32_t o = EMIT ? n1_off[i] : 0u;
         auto test_tile = [&](int64_t tile) {
             const float4 a = __ldg((const float4*)(coarse_aabb + tile * 8));
             const float4 b = __ldg((const float4*)(coarse_aabb + tile * 8) + 1);
             const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
             if (!(lo[0] <= hi[0])) return;   // no samples in this tile
-            if (dgs_cull_pass<D>(rec, lo, hi, 1.0f, 1.0f)) {
+            DgsTileBox box;
+            box.set(lo, hi);
+            if (dgs_cull_pass<D>(rec, box, 1.0f, 1.0f, two_tau)) {
                 if (EMIT) { keys[o] = (uint32_t)tile; vals[o] = (uint32_t)i; o++; }
                 cnt++;
             }
@@ -561,7 +578,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         dgs_for_each_cell<D>(p, r, G, [&](int cell) {
             if (cell >= G.n_ranges) return;
             const int64_t t0 = (int64_t)cell * cpc;
-            if ((rec.flags & DGS_CREC_ALWAYS) || cell >= blocks || T1 < 3) {
+            if (always || cell >= blocks || T1 < 3) {
                 for (int t = 0; t < cpc; t++) test_tile(t0 + t);
                 return;
             }
@@ -577,8 +594,8 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
 #pragma unroll
                 for (int k = -1; k <= 1; k++) {
                     const float m = rec.mu[d] + 2.0f * (float)k - G.off[d];
-                    const float qa = (m - rec.R[d]) / DGS_CELL - (float)cc[d];
-                    const float qb = (m + rec.R[d]) / DGS_CELL - (float)cc[d];
+                    const float qa = (m - recR[d]) / DGS_CELL - (float)cc[d];
+                    const float qb = (m + recR[d]) / DGS_CELL - (float)cc[d];
                     const float slop = 2e-5f + 2e-6f * (fabsf(qa) + fabsf(qb) + (float)cc[d]);
                     const float fa = floorf((qa - slop) * (float)T1) - 1.f;
                     const float fb = floorf((qb + slop) * (float)T1) + 1.f;
@@ -600,8 +617,8 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
     if (!EMIT) n1[i] = cnt;
 }
 
-int dgs_launch_l1(bool emit, const float* means, const float* radii, const DgsCullRec* crec, const dgs_plan_t* plan,
-                  const float* coarse_aabb, uint32_t* n1, const uint32_t* n1_off, uint32_t* keys, uint32_t* vals, cudaStream_t st) {
+int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
+                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* n1, const uint32_t* n1_off, uint32_t* keys, uint32_t* vals, cudaStream_t st) {
     const int64_t P = plan->P;
     if (P <= 0) return 0;
     DgsGrid G;
@@ -609,9 +626,10 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const DgsCu
     G.n_ranges = plan->n_ranges;
     const int nb = dgs_cdiv(P, DGS_THREADS);
     const int cpc = plan->coarse_per_cell;
+    const float two_tau = 2.0f * (plan->tau + DGS_TAU_MAX_EXTRA);
 #define L1_LAUNCH(DD)                                                                                                         \
-    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals); \
-    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals);
+    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals); \
+    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals);
     if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
 #undef L1_LAUNCH
     DGS_NOTE_LAUNCHES(1);
@@ -637,6 +655,75 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_start_kernel(const uint32_
 int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uint32_t* start, cudaStream_t st) {
     const int64_t work = n == 0 ? (int64_t)n_tiles + 1 : n + 1;
     dgs_l1_start_kernel<<<dgs_cdiv(work, DGS_THREADS), DGS_THREADS, 0, st>>>(keys_sorted, n, n_tiles, start);
+    DGS_NOTE_LAUNCHES(1);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// Fine-tile survivor masks: for every coarse-list entry (tile, g) and every function level
+// fn = 0..3 (tau + fn * DGS_TAU_STEP), bit ft says whether Gaussian g can reach power >= -tau
+// somewhere in the box of the samples of fine tile ft of that coarse tile.  Built once per
+// preprocess; the accumulation kernels only test a bit.  masks: [4][n] of u32 / u64.
+// ------------------------------------------------------------------------------------
+template <int D, typename M>
+__global__ void __launch_bounds__(DGS_THREADS) dgs_l1_mask_kernel(const uint32_t* __restrict__ keys_sorted,
+                                                                  const uint32_t* __restrict__ l1_ids, int64_t n,
+                                                                  const float4* __restrict__ crec,
+                                                                  const float* __restrict__ fine_aabb, int fpcD, float tau,
+                                                                  float tau_max, M* __restrict__ masks) {
+    const int64_t e = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
+    if (e >= n) return;
+    const int64_t tile = keys_sorted[e];
+    const DgsCullRecView rec = dgs_crec_load<D>(crec, l1_ids[e]);
+    float sh[4], sh2[4], tt[4], st[4];
+#pragma unroll
+    for (int l = 0; l < 4; l++) {
+        const float tl = tau + DGS_TAU_STEP * (float)l;
+        const float ratio = tl / tau_max;
+        sh2[l] = ratio < 1.f ? ratio * 1.00002f : 1.f;
+        sh[l] = ratio < 1.f ? sqrtf(ratio) * 1.00001f : 1.f;
+        tt[l] = 2.0f * tl;
+        st[l] = sqrtf(tt[l]);
+    }
+    const bool always = rec.rs2 < 0.f;
+    M m[4] = {0, 0, 0, 0};
+    for (int ft = 0; ft < fpcD; ft++) {
+        const float4 a = __ldg((const float4*)(fine_aabb + (tile * fpcD + ft) * 8));
+        const float4 b = __ldg((const float4*)(fine_aabb + (tile * fpcD + ft) * 8) + 1);
+        const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
+        if (!(lo[0] <= hi[0])) continue;   // no samples in this fine tile
+        if (always) {
+#pragma unroll
+            for (int l = 0; l < 4; l++) m[l] |= (M)1 << ft;
+            continue;
+        }
+        DgsTileBox box;
+        box.set(lo, hi);
+        DgsCullGeom<D> g;
+        g.measure(rec, box);
+        if (!g.decide(rec, sh[3], sh2[3], tt[3], st[3])) continue;   // levels are nested: 3 is the widest
+        m[3] |= (M)1 << ft;
+#pragma unroll
+        for (int l = 0; l < 3; l++)
+            if (g.decide(rec, sh[l], sh2[l], tt[l], st[l])) m[l] |= (M)1 << ft;
+    }
+#pragma unroll
+    for (int l = 0; l < 4; l++) masks[(int64_t)l * n + e] = m[l];
+}
+
+int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* keys_sorted, const uint32_t* l1_ids, const float4* crec,
+                        const float* fine_aabb, void* masks, cudaStream_t st) {
+    const int64_t n = (int64_t)plan->n_l1;
+    if (n <= 0) return 0;
+    const int nb = dgs_cdiv(n, DGS_THREADS);
+    const float tau = plan->tau, tau_max = plan->tau + DGS_TAU_MAX_EXTRA;
+    const int f = plan->fine_per_coarse;
+#define MASK_LAUNCH(DD)                                                                                                   \
+    if (plan->mask_bytes == 8) dgs_l1_mask_kernel<DD, unsigned long long><<<nb, DGS_THREADS, 0, st>>>(keys_sorted, l1_ids, n, crec, fine_aabb, f, tau, tau_max, (unsigned long long*)masks); \
+    else dgs_l1_mask_kernel<DD, uint32_t><<<nb, DGS_THREADS, 0, st>>>(keys_sorted, l1_ids, n, crec, fine_aabb, f, tau, tau_max, (uint32_t*)masks);
+    if (plan->D == 1) { MASK_LAUNCH(1) } else if (plan->D == 2) { MASK_LAUNCH(2) } else { MASK_LAUNCH(3) }
+#undef MASK_LAUNCH
     DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;

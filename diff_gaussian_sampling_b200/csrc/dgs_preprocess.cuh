@@ -5,7 +5,7 @@
 int dgs_launch_header_init(DgsDevHeader* h, cudaStream_t st);
 int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, cudaStream_t st);
 int dgs_launch_crec(const float* means, const float* conics, int64_t P, int D, float tau_max, DgsDevHeader* h,
-                    DgsCullRec* crec, cudaStream_t st);
+                    float4* crec, float* crecR, cudaStream_t st);
 int dgs_launch_gauss_preprocess(const float* means, const float* cov, int64_t P, int D, const dgs_plan_t* plan,
                                 float* radii, uint32_t* touched, cudaStream_t st);
 int dgs_launch_duplicate(const float* means, const float* radii, const uint32_t* offsets, int64_t P, int D,
@@ -17,6 +17,8 @@ int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const 
                             const uint32_t* fine_start, uint32_t* fine_ids, float* fine_xyz, cudaStream_t st);
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
                          float* coarse_aabb, cudaStream_t st);
-int dgs_launch_l1(bool emit, const float* means, const float* radii, const DgsCullRec* crec, const dgs_plan_t* plan,
-                  const float* coarse_aabb, uint32_t* n1, const uint32_t* n1_off, uint32_t* keys, uint32_t* vals, cudaStream_t st);
+int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
+                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* n1, const uint32_t* n1_off, uint32_t* keys, uint32_t* vals, cudaStream_t st);
 int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uint32_t* start, cudaStream_t st);
+int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* keys_sorted, const uint32_t* l1_ids, const float4* crec,
+                        const float* fine_aabb, void* masks, cudaStream_t st);

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define DGS_ABI_VERSION 3
+#define DGS_ABI_VERSION 4
 #define DGS_ERR_BAD_ARG 10001
 #define DGS_ERR_UNSUPPORTED 10002
 #define DGS_ERR_BUFFER_TOO_SMALL 10003
@@ -91,7 +91,9 @@ typedef struct dgs_plan {
     uint64_t s_plan_off, s_fine_start_off, s_fine_ids_off, s_fine_xyz_off, s_fine_aabb_off,
              s_coarse_aabb_off, s_tmp_off;
     uint64_t g_prec_off;           /* per-call packed Gaussian records (written by forward/backward) */
-    int32_t  reserved[6];
+    uint64_t g_l1_mask_off;        /* [4 functions][n_l1] fine-tile survivor bitmasks of the coarse-list entries */
+    int32_t  mask_bytes;           /* 4 (fine_per_coarse <= 32) or 8 bytes per mask                              */
+    int32_t  reserved[3];
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
