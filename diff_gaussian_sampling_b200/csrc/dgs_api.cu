@@ -46,7 +46,7 @@ static PublicArrays public_arrays(void* buf, uint64_t L) {
 }
 
 struct GeomLayout {
-    size_t hdr, crec, crecR, touched, offsets, n1, n1_off, scan_tmp, total;
+    size_t hdr, crec, crecR, touched, offsets, n1, n1_off, n1bits, scan_tmp, total;
 };
 static GeomLayout geom_layout(int64_t P, int D = 3) {
     GeomLayout g;
@@ -60,6 +60,7 @@ static GeomLayout geom_layout(int64_t P, int D = 3) {
     g.offsets = o; o = dgs_a128(o + p * 4);
     g.n1 = o; o = dgs_a128(o + p * 4);
     g.n1_off = o; o = dgs_a128(o + p * 4);
+    g.n1bits = o; o = dgs_a128(o + p * 8);
     g.scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes(p));
     g.total = o;
     return g;
@@ -160,7 +161,7 @@ static void gauss_layout(dgs_plan_t* pl) {
 static int choose_tiles(dgs_plan_t* pl) {
     const int D = pl->D;
     const double per_cell = (double)pl->N / (double)(pl->blocks > 0 ? pl->blocks : 1);
-    double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 176.0);
+    double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 110.0);
     if (const char* ev = getenv("DGS_TILE_TARGET")) {          // tuning knob (samples per fine tile)
         const double v = atof(ev);
         if (v >= 8.0) target = v;
@@ -168,7 +169,7 @@ static int choose_tiles(dgs_plan_t* pl) {
     double f = pow(per_cell / target, 1.0 / D);
     int F = (int)floor(f);
     if (F < 1) F = 1;
-    int fpc_default = D == 1 ? 8 : (D == 2 ? 4 : 2);
+    int fpc_default = D == 1 ? 8 : (D == 2 ? 4 : 3);
     if (const char* ev = getenv("DGS_FPC")) {
         const int v = atoi(ev);
         if (v >= 1) fpc_default = v;
@@ -176,7 +177,7 @@ static int choose_tiles(dgs_plan_t* pl) {
     int T1 = (F + fpc_default - 1) / fpc_default;
     // keep a Gaussian's tau-box from covering too many coarse tiles (list entries ~ P * prod(2R/w + 1))
     if (pl->mean_extent > 0.f) {
-        const double k = D == 1 ? 0.765 : (D == 2 ? 0.467 : 0.33);
+        const double k = D == 1 ? 0.765 : (D == 2 ? 0.467 : 0.47);
         int cap = (int)floor(k / (double)pl->mean_extent);
         if (cap < 1) cap = 1;
         if (T1 > cap) T1 = cap;
@@ -333,7 +334,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     if (rc) return rc;
 
     // --- size of the coarse-tile lists ---
-    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, n1, nullptr, nullptr, nullptr, st);
+    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, n1,
+                       (unsigned long long*)(g + gl.n1bits), nullptr, nullptr, nullptr, st);
     if (rc) return rc;
     rc = dgs_exclusive_scan_u32(n1, n1_off, P, gscan, (uint32_t*)&hdr->n_l1, st);
     if (rc) return rc;
@@ -392,7 +394,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     uint32_t* keys_s = (uint32_t*)(tmp + tl.l1_keys_s);
     const float* coarse_aabb = (const float*)(sb + plan->s_coarse_aabb_off);
     if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, nullptr, n1_off, keys_u, vals_u, st);
+        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, nullptr,
+                           (unsigned long long*)(g + gl.n1bits), n1_off, keys_u, vals_u, st);
         if (rc) return rc;
         rc = dgs_sort_pairs_u32(keys_u, vals_u, keys_s, l1_ids, (uint32_t*)(tmp + tl.l1_alt_k), (uint32_t*)(tmp + tl.l1_alt_v),
                                 (int64_t)plan->n_l1, 0, ceil_log2((uint64_t)plan->n_coarse), tmp + tl.l1_sort_tmp, st);

@@ -23,7 +23,7 @@
 #include "dgs_math.cuh"
 
 #ifndef BWD_MINB
-#define BWD_MINB 9
+#define BWD_MINB 0   // 0: let ptxas choose
 #endif
 #define BWD_WARPS 4
 #define BWD_THREADS (BWD_WARPS * 32)
@@ -101,14 +101,9 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
                 dSdC[dgs_tri(D, i, jx)] -= Wv;
             }
     } else if (FN == 3) {
-        int u = 0;
-#pragma unroll
-        for (int i = 0; i < D; i++)
-#pragma unroll
-            for (int jx = i; jx < D; jx++)
-#pragma unroll
-                for (int k = jx; k < D; k++) {
-                    const float Wv = Wu[u++];
+        dgs_for_triples<D, 0, 0, 0>([&](auto ti, auto tj, auto tk) {
+            constexpr int i = decltype(ti)::value, jx = decltype(tj)::value, k = decltype(tk)::value;
+                    const float Wv = Wu[dgs_u3(D, i, jx, k)];
                     const float cij = con[dgs_tri(D, i, jx)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, jx, k)];
                     dSda[k] = fmaf(Wv, fmaf(-a[i], a[jx], cij), dSda[k]);
                     dSda[jx] = fmaf(Wv, fmaf(-a[i], a[k], cik), dSda[jx]);
@@ -116,7 +111,7 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
                     dSdC[dgs_tri(D, i, jx)] = fmaf(Wv, a[k], dSdC[dgs_tri(D, i, jx)]);
                     dSdC[dgs_tri(D, i, k)] = fmaf(Wv, a[jx], dSdC[dgs_tri(D, i, k)]);
                     dSdC[dgs_tri(D, jx, k)] = fmaf(Wv, a[i], dSdC[dgs_tri(D, jx, k)]);
-                }
+        });
     }
 #pragma unroll
     for (int m = 0; m < D; m++) {
@@ -189,6 +184,7 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
 #pragma unroll
         for (int k = 0; k < T; k++) dC[g][k] = 0.f;
     }
+#pragma unroll 2
     for (int s = 0; s < np; s++) {
         float sr[SW];
 #pragma unroll

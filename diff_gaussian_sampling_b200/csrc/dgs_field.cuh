@@ -22,16 +22,12 @@ DGS_HD constexpr int dgs_nuniq(int D, int n) {
     return n == 0 ? 1 : n == 1 ? D : n == 2 ? D * (D + 1) / 2 : D * (D + 1) * (D + 2) / 6;
 }
 DGS_HD constexpr int dgs_ipow(int D, int n) { return n == 0 ? 1 : D * dgs_ipow(D, n - 1); }
-// index of the sorted triple i<=j<=k in lexicographic enumeration
+// index of the sorted triple i<=j<=k in lexicographic enumeration (D <= 3); loop-free so that it folds to
+// a constant after unrolling (a loop here leaves the accumulator index dynamic -> local memory)
 DGS_HD constexpr int dgs_u3(int D, int i, int j, int k) {
-    int u = 0;
-    for (int a = 0; a < D; a++)
-        for (int b = a; b < D; b++)
-            for (int c = b; c < D; c++) {
-                if (a == i && b == j && c == k) return u;
-                u++;
-            }
-    return u;
+    return D == 1 ? 0
+         : D == 2 ? i + j + k
+                  : (i == 0 ? 0 : (i == 1 ? 6 : 9)) + dgs_tri(3, j, k) - dgs_tri(3, i, i);
 }
 DGS_HD constexpr int dgs_u3_any(int D, int i, int j, int k) {
     // sort three indices
@@ -47,6 +43,17 @@ DGS_HD constexpr int dgs_uniq_of(int D, int order, int alpha) {
     if (order == 1) return alpha;
     if (order == 2) return dgs_tri_sym(D, alpha / D, alpha % D);
     return dgs_u3_any(D, alpha / (D * D), (alpha / D) % D, alpha % D);
+}
+
+// Visits the sorted triples i<=j<=k < D in lexicographic order with COMPILE-TIME indices
+// (f(integral_constant i, j, k)); plain unrolled loops leave the array indices dynamic for D == 2.
+template <int V> struct DgsInt { static constexpr int value = V; };
+template <int D, int I, int J, int K, typename F>
+__device__ __forceinline__ void dgs_for_triples(F&& f) {
+    f(DgsInt<I>{}, DgsInt<J>{}, DgsInt<K>{});
+    if constexpr (K + 1 < D) dgs_for_triples<D, I, J, K + 1>(f);
+    else if constexpr (J + 1 < D) dgs_for_triples<D, I, J + 1, J + 1>(f);
+    else if constexpr (I + 1 < D) dgs_for_triples<D, I + 1, I + 1, I + 1>(f);
 }
 
 template <bool EXACT>
@@ -118,20 +125,15 @@ struct DgsPair {
 #pragma unroll
                 for (int j = i; j < D; j++) H[dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
         } else {
-            int u = 0;
-#pragma unroll
-            for (int i = 0; i < D; i++)
-#pragma unroll
-                for (int j = i; j < D; j++)
-#pragma unroll
-                    for (int k = j; k < D; k++) {
-                        const float cij = con[dgs_tri(D, i, j)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, j, k)];
-                        float h = cij * a[k];
-                        h = fmaf(cik, a[j], h);
-                        h = fmaf(cjk, a[i], h);
-                        h = fmaf(-(a[i] * a[j]), a[k], h);
-                        H[u++] = h;
-                    }
+            dgs_for_triples<D, 0, 0, 0>([&](auto ti, auto tj, auto tk) {
+                constexpr int i = decltype(ti)::value, j = decltype(tj)::value, k = decltype(tk)::value;
+                const float cij = con[dgs_tri(D, i, j)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, j, k)];
+                float h = cij * a[k];
+                h = fmaf(cik, a[j], h);
+                h = fmaf(cjk, a[i], h);
+                h = fmaf(-(a[i] * a[j]), a[k], h);
+                H[dgs_u3(D, i, j, k)] = h;
+            });
         }
     }
 };
@@ -195,20 +197,15 @@ __device__ __forceinline__ void dgs_hermite(const float* a, const float* con, fl
 #pragma unroll
             for (int j = i; j < D; j++) H[dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
     } else {
-        int u = 0;
-#pragma unroll
-        for (int i = 0; i < D; i++)
-#pragma unroll
-            for (int j = i; j < D; j++)
-#pragma unroll
-                for (int k = j; k < D; k++) {
+        dgs_for_triples<D, 0, 0, 0>([&](auto ti, auto tj, auto tk) {
+            constexpr int i = decltype(ti)::value, j = decltype(tj)::value, k = decltype(tk)::value;
                     const float cij = con[dgs_tri(D, i, j)], cik = con[dgs_tri(D, i, k)], cjk = con[dgs_tri(D, j, k)];
                     float h = cij * a[k];
                     h = fmaf(cik, a[j], h);
                     h = fmaf(cjk, a[i], h);
                     h = fmaf(-(a[i] * a[j]), a[k], h);
-                    H[u++] = h;
-                }
+                    H[dgs_u3(D, i, j, k)] = h;
+        });
     }
 }
 

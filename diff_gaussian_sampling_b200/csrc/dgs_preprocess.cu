@@ -549,12 +549,14 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
                                                              float two_tau, int64_t P, DgsGrid G, int cpc,
                                                              int T1, int blocks,
                                                              const float* __restrict__ coarse_aabb, uint32_t* __restrict__ n1,
+                                                             unsigned long long* __restrict__ n1bits,
                                                              const uint32_t* __restrict__ n1_off, uint32_t* __restrict__ keys,
                                                              uint32_t* __restrict__ vals) {
     const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
     if (i >= P) return;
     const float r = radii[i];
     uint32_t cnt = 0;
+    unsigned long long bits_out = 0ull;
     if (r > 0.f) {
         float p[D];
 #pragma unroll
@@ -563,14 +565,32 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         const float recR[3] = {crecR[i * 3], crecR[i * 3 + 1], crecR[i * 3 + 2]};
         const bool always = rec.rs2 < 0.f;
         uint32_t o = EMIT ? n1_off[i] : 0u;
+        // The count pass remembers the verdicts of the first 63 enumerated tiles in a bitmask, so that the
+        // emit pass (same enumeration) does not reload the tile boxes and repeat the tests.
+        unsigned long long bits = EMIT ? n1bits[i] : 0ull;
+        const bool use_bits = EMIT && !(bits >> 63);
+        int ci = 0;
+        bool overflow = false;
         auto test_tile = [&](int64_t tile) {
-            const float4 a = __ldg((const float4*)(coarse_aabb + tile * 8));
-            const float4 b = __ldg((const float4*)(coarse_aabb + tile * 8) + 1);
-            const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
-            if (!(lo[0] <= hi[0])) return;   // no samples in this tile
-            DgsTileBox box;
-            box.set(lo, hi);
-            if (dgs_cull_pass<D>(rec, box, 1.0f, 1.0f, two_tau)) {
+            bool pass = false;
+            if (use_bits) {
+                pass = (bits >> ci) & 1ull;
+            } else {
+                const float4 a = __ldg((const float4*)(coarse_aabb + tile * 8));
+                const float4 b = __ldg((const float4*)(coarse_aabb + tile * 8) + 1);
+                const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
+                if (lo[0] <= hi[0]) {        // the tile has samples
+                    DgsTileBox box;
+                    box.set(lo, hi);
+                    pass = dgs_cull_pass<D>(rec, box, 1.0f, 1.0f, two_tau);
+                }
+                if (!EMIT) {
+                    if (ci < 63) bits |= (unsigned long long)pass << ci;
+                    else overflow = true;
+                }
+            }
+            ci++;
+            if (pass) {
                 if (EMIT) { keys[o] = (uint32_t)tile; vals[o] = (uint32_t)i; o++; }
                 cnt++;
             }
@@ -596,9 +616,9 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
                     const float m = rec.mu[d] + 2.0f * (float)k - G.off[d];
                     const float qa = (m - recR[d]) / DGS_CELL - (float)cc[d];
                     const float qb = (m + recR[d]) / DGS_CELL - (float)cc[d];
-                    const float slop = 2e-5f + 2e-6f * (fabsf(qa) + fabsf(qb) + (float)cc[d]);
-                    const float fa = floorf((qa - slop) * (float)T1) - 1.f;
-                    const float fb = floorf((qb + slop) * (float)T1) + 1.f;
+                    const float slop = 1e-4f + 4e-6f * (fabsf(qa) + fabsf(qb) + (float)cc[d]);
+                    const float fa = floorf((qa - slop) * (float)T1);
+                    const float fb = floorf((qb + slop) * (float)T1);
                     if (fb < 0.f || fa > (float)(T1 - 1)) continue;   // this image misses the cell
                     const int ia = fa < 0.f ? 0 : (int)fa;
                     const int ib = fb > (float)(T1 - 1) ? T1 - 1 : (int)fb;
@@ -613,12 +633,14 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
                 for (int ty = tlo[1]; ty <= thi[1]; ty++)
                     for (int tx = tlo[0]; tx <= thi[0]; tx++) test_tile(t0 + ((int64_t)tz * T1 + ty) * T1 + tx);
         });
+        bits_out = overflow ? (1ull << 63) : bits;
     }
-    if (!EMIT) n1[i] = cnt;
+    if (!EMIT) { n1[i] = cnt; n1bits[i] = bits_out; }
 }
 
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
-                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* n1, const uint32_t* n1_off, uint32_t* keys, uint32_t* vals, cudaStream_t st) {
+                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* n1, unsigned long long* n1bits, const uint32_t* n1_off,
+                  uint32_t* keys, uint32_t* vals, cudaStream_t st) {
     const int64_t P = plan->P;
     if (P <= 0) return 0;
     DgsGrid G;
@@ -628,8 +650,8 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const float
     const int cpc = plan->coarse_per_cell;
     const float two_tau = 2.0f * (plan->tau + DGS_TAU_MAX_EXTRA);
 #define L1_LAUNCH(DD)                                                                                                         \
-    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals); \
-    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1_off, keys, vals);
+    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1bits, n1_off, keys, vals); \
+    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, n1, n1bits, n1_off, keys, vals);
     if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
 #undef L1_LAUNCH
     DGS_NOTE_LAUNCHES(1);
