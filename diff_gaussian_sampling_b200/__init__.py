@@ -26,7 +26,7 @@ from ._lib import Plan
 __all__ = [
     "GaussianSampler", "preprocess_gaussians", "preprocess_aggregate", "sample_gaussians",
     "sample_gaussians_derivative", "sample_gaussians_laplacian", "sample_gaussians_third_derivative",
-    "aggregate_neighbors", "plan_of", "count_pairs",
+    "aggregate_neighbors", "plan_of", "count_pairs", "covariances_from_scales_rotations",
 ]
 
 # ---------------------------------------------------------------------------------------
@@ -479,6 +479,51 @@ class GaussianSampler:
         return aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform,
                                    self.indices, self.neighbor_ranges, self.dists, self.densities,
                                    self.inv_total_densities, self.debug)
+
+
+class _CovarianceFromScalesRotations(torch.autograd.Function):
+    """(scales (P,D), rotations) -> (covariances (P,T), conics (P,T)), one fused kernel each way.
+    rotations: D == 2 angle (P,1); D == 3 quaternion wxyz (P,4), normalised inside; D == 1 ignored."""
+
+    @staticmethod
+    def forward(ctx, scales, rotations):
+        lib = _lib.load()
+        scales = _f32c(scales, "scales")
+        P, D = scales.shape
+        T = D * (D + 1) // 2
+        rot = _f32c(rotations, "rotations") if D > 1 else None
+        if D == 2 and rot.numel() != P or D == 3 and rot.shape != (P, 4):
+            raise RuntimeError("rotations must be (P,1) angles for D == 2 and (P,4) quaternions for D == 3")
+        cov = torch.empty(P, T, dtype=torch.float32, device=scales.device)
+        con = torch.empty_like(cov)
+        with torch.cuda.device(scales.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_covariance_forward(scales.data_ptr(), rot.data_ptr() if rot is not None else None, P, D,
+                                                  cov.data_ptr(), con.data_ptr(), st), "dgs_covariance_forward")
+        ctx.save_for_backward(scales, rot if rot is not None else scales.new_empty(0))
+        ctx.rot_shape = tuple(rotations.shape) if rotations is not None else None
+        return cov, con
+
+    @staticmethod
+    def backward(ctx, dcov, dcon):
+        lib = _lib.load()
+        scales, rot = ctx.saved_tensors
+        P, D = scales.shape
+        dcov = _f32c(dcov, "dL_dcovariances") if dcov is not None else torch.zeros(P, D * (D + 1) // 2, device=scales.device)
+        dcon = _f32c(dcon, "dL_dconics") if dcon is not None else torch.zeros_like(dcov)
+        dscales = torch.empty_like(scales)
+        drot = torch.zeros(ctx.rot_shape, dtype=torch.float32, device=scales.device) if ctx.rot_shape is not None else None
+        with torch.cuda.device(scales.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_covariance_backward(scales.data_ptr(), rot.data_ptr() if D > 1 else None, dcov.data_ptr(),
+                                                   dcon.data_ptr(), P, D, dscales.data_ptr(),
+                                                   drot.data_ptr() if (drot is not None and D > 1) else None, st),
+                       "dgs_covariance_backward")
+        return dscales, drot
+
+
+def covariances_from_scales_rotations(scales, rotations=None):
+    return _CovarianceFromScalesRotations.apply(scales, rotations)
 
 
 def count_pairs(binning_buffer, sample_binning_buffer, num_rendered, fn=0) -> int:

@@ -230,6 +230,19 @@ int dgs_aggregate_backward(int64_t P, int D, int L, int K, int E, int n_freq,
                            float* d_features, float* d_transform, float* d_queries, float* d_keys,
                            float* d_frequencies, float* d_distance_transform, void* stream);
 
+/*
+ * ---- (scales, rotations) -> (covariances, conics), fused with its backward ----
+ * Not part of the reference (it takes precomputed covariances/conics, sample_points.cu:37-44; the PIGS caller
+ * builds them with PyTorch autograd): parity unpinned, validated against torch autograd in fp64.
+ * Sigma = R diag(s^2) R^T, conic = R diag(s^-2) R^T, packed row-major upper triangle.  rotations: D == 2 angle (P,1),
+ * D == 3 quaternion (w,x,y,z) (P,4) normalised inside, D == 1 unused (may be NULL).
+ */
+int dgs_covariance_forward(const float* scales_dev, const float* rotations_dev, int64_t P, int D,
+                           float* covariances_dev, float* conics_dev, void* stream);
+int dgs_covariance_backward(const float* scales_dev, const float* rotations_dev, const float* dcovariances_dev,
+                            const float* dconics_dev, int64_t P, int D, float* dscales_dev, float* drotations_dev,
+                            void* stream);
+
 /* Roofline denominators measured live (bench.py): which 0 = FP32 FFMA, 1 = MUFU.EX2.  Launches one
  * kernel on `stream`; *work_out = flop (FFMA counted as 2) resp. ex2 operations of that launch. */
 int dgs_microbench(int which, int iters, float* out_dev, double* work_out, void* stream);
