@@ -427,7 +427,7 @@ def main():
         if r["e2e"]:
             line["e2e"] = {"value": N * world * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": r["e2e"]["h2d"],
                            "d2h_bytes_per_step": r["e2e"]["d2h"], "ms_per_step": e2e_ms / K}
-        if not args.no_cpu_baseline and world >= 1:
+        if not args.no_cpu_baseline and world == 1:   # reported at N=1 only
             try:
                 line["cpu_baseline"] = cpu_port_baseline(args.workload, 16 if P >= 1_000_000 else 32)
             except Exception as ex:  # noqa: BLE001

@@ -286,11 +286,32 @@ __global__ void __launch_bounds__(DGS_THREADS) agg_finish_kernel(const float* __
     const int64_t start = i == 0 ? 0 : ranges[i - 1];
     const int64_t n = ranges[i] - start;
     long long* row = indices + start;
-    for (int64_t a = 1; a < n; a++) {          // insertion sort; rows are short
-        const long long v = row[a];
-        int64_t b = a - 1;
-        while (b >= 0 && row[b] > v) { row[b + 1] = row[b]; b--; }
-        row[b + 1] = v;
+    if (n <= 48) {
+        for (int64_t a = 1; a < n; a++) {          // insertion sort: rows are usually short
+            const long long v = row[a];
+            int64_t b = a - 1;
+            while (b >= 0 && row[b] > v) { row[b + 1] = row[b]; b--; }
+            row[b + 1] = v;
+        }
+    } else {
+        // heap sort for long rows (the reference's 2D radius floor, forward.cu:58, gives ~1e3 neighbours at P = 1M)
+        auto sift = [&](int64_t root, int64_t end) {
+            const long long v = row[root];
+            for (;;) {
+                int64_t c = 2 * root + 1;
+                if (c >= end) break;
+                if (c + 1 < end && row[c + 1] > row[c]) c++;
+                if (!(row[c] > v)) break;
+                row[root] = row[c];
+                root = c;
+            }
+            row[root] = v;
+        };
+        for (int64_t a = n / 2 - 1; a >= 0; a--) sift(a, n);
+        for (int64_t e = n - 1; e > 0; e--) {
+            const long long t = row[0]; row[0] = row[e]; row[e] = t;
+            sift(0, e);
+        }
     }
     float mine[D];
 #pragma unroll

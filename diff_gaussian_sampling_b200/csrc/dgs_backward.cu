@@ -25,6 +25,9 @@
 #ifndef BWD_MINB
 #define BWD_MINB 0   // 0: let ptxas choose
 #endif
+#ifndef BWD_TUNED
+#define BWD_TUNED 7   // CTAs per SM of the 2D single-channel gaussian kernel (measured: 7 beats 8, 9, 10; profiles/r01_sweep_occupancy.jsonl)
+#endif
 #define BWD_WARPS 4
 #define BWD_THREADS (BWD_WARPS * 32)
 #define BWD_QF 96    // fast-id queue slots per warp
@@ -260,7 +263,7 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
 }
 
 template <int D, int FN, int CB, bool VPOST>
-__global__ void __launch_bounds__(BWD_THREADS, BWD_MINB) dgs_backward_kernel(const BwdArgs A) {
+__global__ void __launch_bounds__(BWD_THREADS, (D <= 2 && FN == 0 && CB == 1) ? BWD_TUNED : BWD_MINB) dgs_backward_kernel(const BwdArgs A) {
     using K = BwdCfg<D, FN, CB>;
     constexpr int U = K::U, AFULL = K::AFULL, SW = K::SW, SW0 = K::SW0, SCAP = K::SCAP, NG = K::G;
     constexpr int PW = DGS_PREC_W(D);

@@ -113,6 +113,12 @@ def _own_case(name):
         m[:40, 0] = rng.uniform(0.97, 1.06, 40).astype(f)
         m[40:80, 0] = rng.uniform(-1.06, -0.97, 40).astype(f)
         return m, con, radii, cases.aggregate_inputs(P, 2, L=33, K=7, n_freq=3)
+    if name == "d2_long_rows":
+        # rows longer than the insertion-sort cut-off (heap-sort path): few, large, overlapping Gaussians
+        P = 400
+        m, v, cov, con = cases.make_gaussians(rng, P, 2, 1, 0.2, spread=0.3)
+        radii = rng.uniform(1.0, 2.0, P).astype(f)
+        return m, con, radii, cases.aggregate_inputs(P, 2, L=4, K=3)
     if name == "d1_far":
         # means spread over more than one period: |dx| >= 2 takes the fmod arm
         P = 300
@@ -124,7 +130,7 @@ def _own_case(name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["d3", "d2_p3000", "d2_mixed_sizes_seam", "d1_far"])
+@pytest.mark.parametrize("name", ["d3", "d2_p3000", "d2_mixed_sizes_seam", "d1_far", "d2_long_rows"])
 def test_product_aggregate_vs_cpu_oracle(name):
     m, con, radii, a = _own_case(name)
     got = run_product_aggregate(m, con, radii, a)
