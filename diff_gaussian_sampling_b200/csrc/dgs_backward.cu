@@ -25,6 +25,14 @@
 #ifndef BWD_MINB
 #define BWD_MINB 0   // 0: let ptxas choose
 #endif
+#define DGS_PRAGMA_(x) _Pragma(#x)
+#define DGS_UNROLL(n) DGS_PRAGMA_(unroll n)
+#ifndef BWD_PACKED
+#define BWD_PACKED 0          // FFMA2/FMUL2/FADD2 over the lane's two Gaussians: measured SLOWER (2.99 vs 2.81 ms, profiles/r01_sweep_packed_backward.jsonl); kept for reference
+#endif
+#ifndef BWD_PACKED_UNROLL
+#define BWD_PACKED_UNROLL 2
+#endif
 #ifndef BWD_TUNED
 #define BWD_TUNED 7   // CTAs per SM of the 2D single-channel gaussian kernel (measured: 7 beats 8, 9, 10; profiles/r01_sweep_occupancy.jsonl)
 #endif
@@ -187,6 +195,42 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
 #pragma unroll
         for (int k = 0; k < T; k++) dC[g][k] = 0.f;
     }
+    if constexpr (BWD_PACKED && FN == 0 && FAST && VPOST && NG == 2 && CB == 1) {
+        // packed path: the lane's two Gaussians ride in the two halves of FFMA2/FMUL2/FADD2 operands.
+        // Xn = x - mu = -X exactly; squares and products of two Xn are sign-free, the first moment is negated at the end.
+        float2 nmu[D], g2[T], dV2 = make_float2(0.f, 0.f), dMn[D], dC2[T];
+#pragma unroll
+        for (int d = 0; d < D; d++) { nmu[d] = make_float2(-mu[0][d], -mu[1][d]); dMn[d] = make_float2(0.f, 0.f); }
+#pragma unroll
+        for (int k = 0; k < T; k++) { g2[k] = make_float2(geo[0][k], geo[1][k]); dC2[k] = make_float2(0.f, 0.f); }
+DGS_UNROLL(BWD_PACKED_UNROLL)
+        for (int s = 0; s < np; s++) {
+            const float4 v = *(const float4*)(sS + s * SW);
+            const float sr[4] = {v.x, v.y, v.z, v.w};
+            float2 Xn[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) Xn[d] = __fadd2_rn(dgs_bc2(sr[d]), nmu[d]);
+            const float2 t = dgs_white_t2<D>(Xn, g2);
+            const float2 Gv = make_float2(dgs_ex2(-t.x), dgs_ex2(-t.y));
+            const float2 w = __fmul2_rn(Gv, dgs_bc2(sr[D]));
+            dV2 = __fadd2_rn(dV2, w);
+            float2 wX[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                wX[d] = __fmul2_rn(w, Xn[d]);
+                dMn[d] = __fadd2_rn(dMn[d], wX[d]);
+            }
+#pragma unroll
+            for (int i = 0; i < D; i++)
+#pragma unroll
+                for (int j = i; j < D; j++) dC2[dgs_tri(D, i, j)] = __ffma2_rn(wX[i], Xn[j], dC2[dgs_tri(D, i, j)]);
+        }
+        dV[0][0] = dV2.x; dV[1][0] = dV2.y;
+#pragma unroll
+        for (int d = 0; d < D; d++) { dM[0][d] = -dMn[d].x; dM[1][d] = -dMn[d].y; }
+#pragma unroll
+        for (int k = 0; k < T; k++) { dC[0][k] = dC2[k].x; dC[1][k] = dC2[k].y; }
+    } else {
 #pragma unroll 2
     for (int s = 0; s < np; s++) {
         float sr[SW];
@@ -249,6 +293,7 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
             }
         }
     }
+    }   // scalar path
 #pragma unroll
     for (int g = 0; g < NG; g++) {
         if (valid[g]) {

@@ -171,6 +171,28 @@ __device__ __forceinline__ float dgs_white_G(const float* X, const float* U) {
     return dgs_ex2(np);
 }
 
+// Packed (two-lane) form of the same: |U X|^2 for two pairs at once with FFMA2/FMUL2 (sm_100 packed FP32: one issue
+// slot, two fp32 results, each rounded exactly like the scalar instruction).  The accumulation kernels are bound by
+// issue slots and by the FMA pipe, not by flops alone; packing two samples (forward) or two Gaussians (backward) halves
+// the issue slots of the FP32 part (tools/mb/mb_fwdloop.cu: 13.5 -> 11.3 cycles per warp-pair for the bare loop).
+__device__ __forceinline__ float2 dgs_bc2(float v) { return make_float2(v, v); }
+template <int D>
+__device__ __forceinline__ float2 dgs_white_t2(const float2* X, const float2* U) {
+    if (D == 1) {
+        const float2 y = __fmul2_rn(U[0], X[0]);
+        return __fmul2_rn(y, y);
+    } else if (D == 2) {
+        const float2 y0 = __ffma2_rn(U[1], X[1], __fmul2_rn(U[0], X[0]));
+        const float2 y1 = __fmul2_rn(U[2], X[1]);
+        return __ffma2_rn(y0, y0, __fmul2_rn(y1, y1));
+    } else {
+        const float2 y0 = __ffma2_rn(U[2], X[2], __ffma2_rn(U[1], X[1], __fmul2_rn(U[0], X[0])));
+        const float2 y1 = __ffma2_rn(U[4], X[2], __fmul2_rn(U[3], X[1]));
+        const float2 y2 = __fmul2_rn(U[5], X[2]);
+        return __ffma2_rn(y0, y0, __ffma2_rn(y1, y1, __fmul2_rn(y2, y2)));
+    }
+}
+
 // a = C X from the packed conic
 template <int D>
 __device__ __forceinline__ void dgs_conic_times(const float* con, const float* X, float* a) {

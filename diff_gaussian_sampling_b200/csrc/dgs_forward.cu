@@ -67,6 +67,46 @@ __device__ __forceinline__ void fwd_eval_fast(const float* __restrict__ sF, int 
                                               float (&acc)[FwdCfg<D, FN, CB>::SMAX][FwdCfg<D, FN, CB>::U][CB]) {
     using K = FwdCfg<D, FN, CB>;
     constexpr int T = K::T, U = K::U, FW = K::FW;
+    if constexpr (FN == 0 && CB == 1) {
+        // packed path: samples (2p, 2p+1) of the lane ride in the two halves of FFMA2/FMUL2/FADD2 operands
+        // (bit-identical to the scalar form: every half is rounded like the scalar instruction).
+        constexpr int SP = (S + 1) / 2;
+        float2 nx[SP][D], a2[SP];
+#pragma unroll
+        for (int p = 0; p < SP; p++) {
+            const int i0 = 2 * p, i1 = (2 * p + 1 < S) ? 2 * p + 1 : 2 * p;
+#pragma unroll
+            for (int d = 0; d < D; d++) nx[p][d] = make_float2(-x[i0][d], -x[i1][d]);
+            a2[p] = make_float2(acc[i0][0][0], (2 * p + 1 < S) ? acc[i1][0][0] : 0.f);
+        }
+        for (int k = 0; k < nf; k++) {
+            float r[FW];
+#pragma unroll
+            for (int q = 0; q < FW / 2; q++) {
+                const float2 v = *(const float2*)(sF + k * FW + q * 2);
+                r[q * 2] = v.x; r[q * 2 + 1] = v.y;
+            }
+            float2 U2[T];
+#pragma unroll
+            for (int t = 0; t < T; t++) U2[t] = dgs_bc2(r[D + t]);
+            const float2 val2 = dgs_bc2(r[D + T]);
+#pragma unroll
+            for (int p = 0; p < SP; p++) {
+                float2 X[D];
+#pragma unroll
+                for (int d = 0; d < D; d++) X[d] = __fadd2_rn(dgs_bc2(r[d]), nx[p][d]);
+                const float2 t2 = dgs_white_t2<D>(X, U2);
+                const float2 G = make_float2(dgs_ex2(-t2.x), dgs_ex2(-t2.y));
+                a2[p] = __ffma2_rn(val2, G, a2[p]);
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < SP; p++) {
+            acc[2 * p][0][0] = a2[p].x;
+            if (2 * p + 1 < S) acc[2 * p + 1][0][0] = a2[p].y;
+        }
+        return;
+    }
     for (int k = 0; k < nf; k++) {
         float r[FW];
 #pragma unroll

@@ -24,6 +24,8 @@ def main():
     rng = np.random.default_rng(0)
     m, v, cov, con = cases.make_gaussians(rng, P, D, C, cases.sigma_for(P, D))
     s = cases.grid_samples(n, D)
+    if os.environ.get("DGS_QUICK_PERMUTE"):          # same points in a fixed random order (SURVEY.md §8d secondary run)
+        s = np.ascontiguousarray(s[np.random.default_rng(1).permutation(s.shape[0])])
     dev = torch.device("cuda:0")
     tm, tv, tcov, tcon, ts = (torch.from_numpy(x).to(dev) for x in (m, v, cov, con, s))
     N = s.shape[0]
