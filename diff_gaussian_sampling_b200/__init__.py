@@ -36,6 +36,7 @@ __all__ = [
 # ---------------------------------------------------------------------------------------
 _PLANS: "OrderedDict[tuple, Plan]" = OrderedDict()
 _PLANS_MAX = 64
+_SAMPLE_PLANS: "OrderedDict[tuple, Plan]" = OrderedDict()     # sample_binning_buffer -> plan it was built with
 
 
 def _remember(buf: torch.Tensor, plan: Plan):
@@ -78,7 +79,9 @@ class _NativeOps:
 
     # -- preprocess_gaussians (sample_points.cu:37-98) ----------------------------------
     @staticmethod
-    def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None):
+    def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None, reuse=None):
+        """reuse = (sample_binning_buffer, sample_ranges) of an earlier call on the SAME samples: the sample side of
+        the binning (sampleWithKeys / sort / ranges and the internal tile order) is carried over instead of rebuilt."""
         lib = _lib.load()
         means = _f32c(means, "means"); covariances = _f32c(covariances, "covariances")
         conics = _f32c(conics, "conics"); samples = _f32c(samples, "samples")
@@ -102,8 +105,16 @@ class _NativeOps:
             _lib.check(lib.dgs_plan_begin(means.data_ptr(), conics.data_ptr(), samples.data_ptr(), P, N, D, bptr,
                                           float(tau) if tau else 0.0, geom.data_ptr(), geom.numel(),
                                           ctypes.byref(plan), st), "dgs_plan_begin")
-            sbuf = torch.empty(plan.sample_binning_bytes, **u8)
-            sample_ranges = torch.zeros(plan.ranges_bytes, **u8)          # sample_points.cu:77
+            sbuf = sample_ranges = None
+            if reuse is not None:
+                prev_sbuf, prev_sranges = reuse
+                prev = _SAMPLE_PLANS.get((dev.index, prev_sbuf.data_ptr(), prev_sbuf.numel()))
+                if prev is not None and \
+                        lib.dgs_plan_reuse_samples(ctypes.byref(plan), ctypes.byref(prev)) == 0:
+                    sbuf, sample_ranges = prev_sbuf, prev_sranges
+            if sbuf is None:
+                sbuf = torch.empty(plan.sample_binning_bytes, **u8)
+                sample_ranges = torch.zeros(plan.ranges_bytes, **u8)      # sample_points.cu:77
             _lib.check(lib.dgs_preprocess_count(ctypes.byref(plan), means.data_ptr(), covariances.data_ptr(),
                                                 samples.data_ptr(), radii.data_ptr(), geom.data_ptr(), geom.numel(),
                                                 sbuf.data_ptr(), sbuf.numel(), sample_ranges.data_ptr(), st),
@@ -116,6 +127,9 @@ class _NativeOps:
             if debug:
                 torch.cuda.synchronize(dev)                    # CHECK_CUDA semantics (auxiliary.h:33-40)
         _remember(gbuf, plan)
+        _SAMPLE_PLANS[(dev.index, sbuf.data_ptr(), sbuf.numel())] = plan
+        while len(_SAMPLE_PLANS) > _PLANS_MAX:
+            _SAMPLE_PLANS.popitem(last=False)
         return int(plan.num_rendered), gbuf, sbuf, ranges, sample_ranges, radii
 
     # -- forward (sample_points.cu:100-143,198-297) -------------------------------------
@@ -331,9 +345,9 @@ def sample_gaussians_third_derivative(debug, *args):
     return _SampleGaussiansThirdDerivative.apply(debug, *args)
 
 
-def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None):
+def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None, reuse=None):
     args = (means, values, covariances, conics, samples, debug)
-    return call_debug(_C.preprocess_gaussians, debug, "preprocess", *args, bounds=bounds, tau=tau)
+    return call_debug(_C.preprocess_gaussians, debug, "preprocess", *args, bounds=bounds, tau=tau, reuse=reuse)
 
 
 def preprocess_aggregate(means, conics, radii, debug):
@@ -434,9 +448,21 @@ class GaussianSampler:
     def __init__(self, debug=False):
         self.debug = debug
 
-    def preprocess(self, means, values, covariances, conics, samples, bounds=None):
+    def preprocess(self, means, values, covariances, conics, samples, bounds=None, reuse_sample_binning=False):
+        """reuse_sample_binning=True: the caller states that `samples` holds the same points as in the previous
+        preprocess() of this object (fixed collocation points); their binning is then carried over."""
+        reuse = None
+        if reuse_sample_binning and getattr(self, "sample_binning_buffer", None) is not None \
+                and self.sample_binning_buffer.numel() and self.samples.shape == samples.shape:
+            reuse = (self.sample_binning_buffer, self.sample_ranges)
+            if bounds is None:
+                bounds = self._bounds
         num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii = \
-            preprocess_gaussians(means, values, covariances, conics, samples, self.debug, bounds=bounds)
+            preprocess_gaussians(means, values, covariances, conics, samples, self.debug, bounds=bounds, reuse=reuse)
+        if binning_buffer.numel():
+            pl = plan_of(binning_buffer, num_rendered)
+            D = means.shape[-1]
+            self._bounds = (list(pl.lo)[:D], list(pl.hi)[:D])
         self.means = means
         self.values = values
         self.conics = conics

@@ -32,7 +32,7 @@ class Plan(ctypes.Structure):
         ("g_sort_tmp_off", c_u64),
         ("s_plan_off", c_u64), ("s_fine_start_off", c_u64), ("s_fine_ids_off", c_u64), ("s_fine_xyz_off", c_u64),
         ("s_fine_aabb_off", c_u64), ("s_coarse_aabb_off", c_u64), ("s_tmp_off", c_u64),
-        ("g_prec_off", c_u64), ("g_l1_mask_off", c_u64), ("mask_bytes", c_i32), ("reserved", c_i32 * 3),
+        ("g_prec_off", c_u64), ("g_l1_mask_off", c_u64), ("mask_bytes", c_i32), ("samples_reused", c_i32), ("reserved", c_i32 * 2),
     ]
 
     def as_dict(self):
@@ -55,6 +55,7 @@ EXPORTS = {
                                       ctypes.POINTER(Plan), c_vp]),
     "dgs_preprocess_count": (ctypes.c_int, [ctypes.POINTER(Plan), c_vp, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp, c_sz, c_vp, c_vp]),
     "dgs_preprocess_bin": (ctypes.c_int, [ctypes.POINTER(Plan), c_vp, c_vp, c_vp, c_sz, c_vp, c_sz, c_vp, c_sz, c_vp, c_vp]),
+    "dgs_plan_reuse_samples": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.POINTER(Plan)]),
     "dgs_plan_from_buffer": (ctypes.c_int, [c_vp, c_sz, c_u32, ctypes.POINTER(Plan), c_vp]),
     "dgs_sample_forward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
                                           c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

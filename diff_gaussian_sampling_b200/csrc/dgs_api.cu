@@ -187,6 +187,18 @@ static int choose_tiles(dgs_plan_t* pl) {
         if (v >= 1) T1 = v;
     }
     if (T1 < 1) T1 = 1;
+    // small problems: one CTA works on one coarse tile, so trade fine tiles per coarse tile for more coarse tiles
+    // until the grid can fill the 148 SMs (cfg1: 21 -> 189 CTAs)
+    {
+        auto ipow_ = [](int64_t b, int e) { int64_t r = 1; for (int i = 0; i < e; i++) r *= b; return r; };
+        int t1_cap = F;
+        if (pl->mean_extent > 0.f) {
+            const double k = D == 1 ? 0.765 : (D == 2 ? 0.467 : 0.47);
+            const int cap = (int)floor(k / (double)pl->mean_extent);
+            t1_cap = cap < 1 ? 1 : (cap < F ? cap : F);
+        }
+        while (T1 < t1_cap && (int64_t)pl->blocks * ipow_(T1, D) < 2 * 148 && !getenv("DGS_T1")) T1++;
+    }
     int fpc = (F + T1 - 1) / T1;
     const int fpc_max = D == 1 ? 64 : (D == 2 ? 8 : 4);
     if (fpc > fpc_max) fpc = fpc_max;
@@ -267,6 +279,22 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
     return 0;
 }
 
+extern "C" __attribute__((visibility("default"))) int dgs_plan_reuse_samples(dgs_plan_t* plan, const dgs_plan_t* prev) {
+    DGS_REQUIRE(plan && prev && plan->magic == DGS_PLAN_MAGIC && prev->magic == DGS_PLAN_MAGIC && prev->abi == DGS_ABI_VERSION,
+                DGS_ERR_BAD_PLAN, "bad plan");
+    bool same = plan->D == prev->D && plan->N == prev->N && plan->blocks == prev->blocks && prev->n_fine > 0;
+    for (int d = 0; d < 3; d++)
+        same = same && plan->grid[d] == prev->grid[d] && plan->lo[d] == prev->lo[d] && plan->hi[d] == prev->hi[d];
+    DGS_REQUIRE(same, DGS_ERR_BAD_ARG, "the previous plan was built for different samples (N, D, bounds or cell grid)");
+    plan->T1 = prev->T1; plan->fpc = prev->fpc; plan->F = prev->F;
+    plan->coarse_per_cell = prev->coarse_per_cell; plan->fine_per_coarse = prev->fine_per_coarse;
+    plan->n_coarse = prev->n_coarse; plan->n_fine = prev->n_fine;
+    sample_layout(plan);
+    DGS_REQUIRE(plan->sample_binning_bytes == prev->sample_binning_bytes, DGS_ERR_BAD_ARG, "sample buffer layouts differ");
+    plan->samples_reused = 1;
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------
 // step 2: counts (Gaussian side) + the whole sample side
 // ---------------------------------------------------------------------------------------
@@ -317,21 +345,24 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     float* coarse_aabb = (float*)(sb + plan->s_coarse_aabb_off);
     uint32_t* tile_of = (uint32_t*)(stmp + tl.tile_of);
     uint32_t* rank_of = (uint32_t*)(stmp + tl.rank_of);
-    DGS_CUDA(cudaMemsetAsync(fine_start, 0, ((size_t)plan->n_fine + 1) * 4, st));
-    rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr, st);
-    if (rc) return rc;
-    rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
-    if (rc) return rc;
-    rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
-    if (rc) return rc;
-    rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
-    if (rc) return rc;
-    // public sorted sample list: stable sort on the cell bits == sort on bits [0, 32+bit)
-    rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(stmp + tl.alt_keys),
-                            (uint32_t*)(stmp + tl.alt_vals), N, 32, 32 + plan->sort_bits, stmp + tl.sort_tmp, st);
-    if (rc) return rc;
-    rc = dgs_launch_ranges(pa.keys, N, sample_ranges_dev, plan->n_ranges, st);
-    if (rc) return rc;
+    if (!plan->samples_reused) {
+        DGS_CUDA(cudaMemsetAsync(fine_start, 0, ((size_t)plan->n_fine + 1) * 4, st));
+        rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr, st);
+        if (rc) return rc;
+        rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
+        if (rc) return rc;
+        rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
+        if (rc) return rc;
+        rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
+        if (rc) return rc;
+        // public sorted sample list: stable sort on the cell bits == sort on bits [0, 32+bit)
+        rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(stmp + tl.alt_keys),
+                                (uint32_t*)(stmp + tl.alt_vals), N, 32, 32 + plan->sort_bits, stmp + tl.sort_tmp, st);
+        if (rc) return rc;
+        rc = dgs_launch_ranges(pa.keys, N, sample_ranges_dev, plan->n_ranges, st);
+        if (rc) return rc;
+
+    }
 
     // --- size of the coarse-tile lists ---
     rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, n1,

@@ -93,7 +93,8 @@ typedef struct dgs_plan {
     uint64_t g_prec_off;           /* per-call packed Gaussian records (written by forward/backward) */
     uint64_t g_l1_mask_off;        /* [4 functions][n_l1] fine-tile survivor bitmasks of the coarse-list entries */
     int32_t  mask_bytes;           /* 4 (fine_per_coarse <= 32) or 8 bytes per mask                              */
-    int32_t  reserved[3];
+    int32_t  samples_reused;       /* 1: the sample side of the buffers was carried over (dgs_plan_reuse_samples) */
+    int32_t  reserved[2];
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
@@ -153,6 +154,16 @@ int dgs_preprocess_bin(const dgs_plan_t* plan, const float* means_dev, const flo
                        void* binning_dev, size_t binning_bytes,
                        void* sample_binning_dev, size_t sample_binning_bytes,
                        void* ranges_dev, void* stream);
+
+/*
+ * Optional, between dgs_plan_begin and dgs_preprocess_count (no reference counterpart: the
+ * reference re-bins the samples in every preprocess, sampler_impl.cu:294-327, although that part never reads Gaussian
+ * data).  When the query points have not changed since `previous` was built — same N, D, bounds and cell grid —
+ * the plan takes over the previous tile hierarchy and sample-buffer layout and dgs_preprocess_count then skips the
+ * whole sample side: the caller passes the SAME sample_binning_dev / sample_ranges_dev as before (left untouched).
+ * Returns DGS_ERR_BAD_ARG if the two plans are not compatible (the caller then simply does not reuse).
+ */
+int dgs_plan_reuse_samples(dgs_plan_t* plan, const dgs_plan_t* previous);
 
 /* Recovers the plan stored inside binning_dev (L = num_rendered entries).  Synchronises. */
 int dgs_plan_from_buffer(const void* binning_dev, size_t binning_bytes, uint32_t num_rendered,

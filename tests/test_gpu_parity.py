@@ -82,3 +82,41 @@ def test_empty_inputs():
     assert nr == 0 and radii.numel() == 0
     out = dgs.sample_gaussians(z(0, 2), z(0, 1), z(0, 3), z(10, 2), nr, gb, sb, r, sr, False)
     assert out.shape == (10, 1) and float(out.abs().sum()) == 0.0
+
+
+def test_reuse_of_sample_binning_matches_fresh_preprocess():
+    """with fixed query points the sample side of the binning is carried over; the Gaussians move
+    between the two preprocess() calls.  Public arrays must equal those of a fresh preprocess bit for bit, fields and
+    gradients within the usual tolerances (the internal tile hierarchy may differ, so culled terms may differ)."""
+    import torch
+    import diff_gaussian_sampling_b200 as dgs
+    c = cases.case("d2_dense_small")
+    dev = torch.device("cuda:0")
+    t = {k: torch.from_numpy(v).to(dev) for k, v in c.items()}
+    s = dgs.GaussianSampler()
+    s.preprocess(t["means"], t["values"], t["covariances"], t["conics"], t["samples"])
+    sb_ptr = s.sample_binning_buffer.data_ptr()
+    rng = np.random.default_rng(3)
+    c2 = dict(c)
+    c2["means"] = (c["means"] + rng.normal(size=c["means"].shape).astype(np.float32) * 0.01).astype(np.float32)
+    m2 = torch.from_numpy(c2["means"]).to(dev).requires_grad_(True)
+    v2 = t["values"].clone().requires_grad_(True)
+    cn2 = t["conics"].clone().requires_grad_(True)
+    s.preprocess(m2, v2, t["covariances"], cn2, t["samples"], reuse_sample_binning=True)
+    assert s.sample_binning_buffer.data_ptr() == sb_ptr, "sample binning was rebuilt"
+    assert dgs.plan_of(s.binning_buffer, s.num_rendered).samples_reused == 1
+    out = s.sample_gaussians()
+    g = cases.grad_out("reuse", 0, c["samples"].shape[0], 2, 1)
+    out.backward(torch.from_numpy(g).to(dev))
+    fresh = parity.run_product(c2, fns=(0,), name="reuse", douts={"gaussian": g})
+    got = dict(num_rendered=s.num_rendered, radii=s.radii.cpu().numpy(),
+               ranges=s.ranges.cpu().numpy().view(np.uint32).reshape(-1, 2),
+               sample_ranges=s.sample_ranges.cpu().numpy().view(np.uint32).reshape(-1, 2))
+    for k, v in parity.split_public(s.binning_buffer, s.num_rendered).items():
+        got["g_" + k] = v
+    for k, v in parity.split_public(s.sample_binning_buffer, c["samples"].shape[0]).items():
+        got["s_" + k] = v
+    parity.assert_binning_equal(got, fresh, "reuse")
+    assert parity.norm_err(out.detach().cpu().numpy(), fresh["out_gaussian"].astype(np.float64)) <= 1e-6
+    for k, tt in (("dmeans_", m2), ("dvalues_", v2), ("dconics_", cn2)):
+        assert parity.bwd_err(tt.grad.cpu().numpy(), fresh[k + "gaussian"].astype(np.float64)) <= 1e-5
