@@ -160,7 +160,10 @@ static void gauss_layout(dgs_plan_t* pl) {
 // ---------------------------------------------------------------------------------------
 static int choose_tiles(dgs_plan_t* pl) {
     const int D = pl->D;
-    const double per_cell = (double)pl->N / (double)(pl->blocks > 0 ? pl->blocks : 1);
+    // samples per OCCUPIED cell: a point shard spans only part of the (global) bounding box
+    double cells_eff = (double)(pl->blocks > 0 ? pl->blocks : 1) * ((double)pl->reserved0 * 1e-6);
+    if (cells_eff < 1.0) cells_eff = 1.0;
+    const double per_cell = (double)pl->N / cells_eff;
     double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 110.0);
     if (const char* ev = getenv("DGS_TILE_TARGET")) {          // tuning knob (samples per fine tile)
         const double v = atof(ev);
@@ -238,8 +241,11 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
     if (bounds_host) {
         DGS_CUDA(cudaMemcpyAsync(hdr->lo, bounds_host, sizeof(float) * D, cudaMemcpyHostToDevice, st));
         DGS_CUDA(cudaMemcpyAsync(hdr->hi, bounds_host + D, sizeof(float) * D, cudaMemcpyHostToDevice, st));
+        // the extent of THIS call's samples (a rank's shard) still sizes the tiles: reduce it, but keep the given bounds
+        rc = dgs_launch_bounds(samples_dev, N, D, hdr, false, st);
+        if (rc) return rc;
     } else {
-        rc = dgs_launch_bounds(samples_dev, N, D, hdr, st);
+        rc = dgs_launch_bounds(samples_dev, N, D, hdr, true, st);
         if (rc) return rc;
     }
     rc = dgs_launch_crec(means_dev, conics_dev, P, D, plan->tau + DGS_TAU_MAX_EXTRA, hdr, (float4*)(g + gl.crec),
@@ -271,6 +277,19 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
     if (D > 2) ext_cells += (int64_t)plan->grid[2] * plan->grid[1] * plan->grid[0];
     plan->n_cells_ext = (int)(ext_cells + 1);
     plan->mean_extent = h.extent_cnt ? (float)(h.extent_sum / (double)h.extent_cnt) : 0.f;
+    // fraction of the bounding box that this call's samples span (1 unless the caller supplied wider, global bounds)
+    double occupied = 1.0;
+    for (int d = 0; d < D; d++) {
+        auto ord2f = [](uint32_t u) { uint32_t b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; float f; memcpy(&f, &b, 4); return f; };
+        const float llo = ord2f(h.lo_bits[d]), lhi = ord2f(h.hi_bits[d]);
+        const double ext = (double)h.hi[d] - (double)h.lo[d];
+        if (ext > 0.0 && lhi >= llo) {
+            double f = ((double)lhi - (double)llo) / ext;
+            f = f < 1e-3 ? 1e-3 : (f > 1.0 ? 1.0 : f);
+            occupied *= f;
+        }
+    }
+    plan->reserved0 = (int32_t)(occupied * 1e6);
     plan->exact_wrap = (h.flags & DGS_HDR_EXACT_WRAP) ? 1 : 0;
     rc = choose_tiles(plan);
     if (rc) return rc;

@@ -59,15 +59,14 @@ __global__ void dgs_bounds_finalize_kernel(DgsDevHeader* h, int D) {
     }
 }
 
-int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, cudaStream_t st) {
+int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, bool finalize, cudaStream_t st) {
     const int64_t n_flat = N * D;
     int nb = dgs_cdiv(n_flat, (int64_t)DGS_THREADS * 8);
     nb = nb < 3 ? 3 : (nb > 148 * 12 ? 148 * 12 : ((nb + 2) / 3) * 3);
     if (D == 1) dgs_bounds_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
     else if (D == 2) dgs_bounds_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
     else dgs_bounds_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
-    dgs_bounds_finalize_kernel<<<1, 32, 0, st>>>(h, D);
-    DGS_NOTE_LAUNCHES(1);
+    if (finalize) { dgs_bounds_finalize_kernel<<<1, 32, 0, st>>>(h, D); DGS_NOTE_LAUNCHES(1); }
     DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;

@@ -3,7 +3,8 @@
 #include "dgs_common.cuh"
 
 int dgs_launch_header_init(DgsDevHeader* h, cudaStream_t st);
-int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, cudaStream_t st);
+// finalize: also publish the reduced bounds as h->lo / h->hi (otherwise only h->lo_bits / h->hi_bits are written)
+int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, bool finalize, cudaStream_t st);
 int dgs_launch_crec(const float* means, const float* conics, int64_t P, int D, float tau_max, DgsDevHeader* h,
                     float4* crec, float* crecR, cudaStream_t st);
 int dgs_launch_gauss_preprocess(const float* means, const float* cov, int64_t P, int D, const dgs_plan_t* plan,

@@ -80,7 +80,7 @@ typedef struct dgs_plan {
     int32_t  n_fine;           /* n_coarse * fpc^D                                     */
     uint64_t n_l1;             /* entries of the coarse-tile Gaussian lists            */
     float    mean_extent;      /* mean tau-bbox half width (statistic used to pick T1) */
-    int32_t  reserved0;
+    int32_t  reserved0;        /* 1e6 x fraction of the bounding box spanned by this call's samples (tile sizing) */
     /* buffer sizes */
     uint64_t geom_bytes;           /* phase scratch (reference: GeometryState)         */
     uint64_t binning_bytes;        /* binning_buffer (valid after dgs_preprocess_count)*/
