@@ -26,7 +26,7 @@ from ._lib import Plan
 __all__ = [
     "GaussianSampler", "preprocess_gaussians", "preprocess_aggregate", "sample_gaussians",
     "sample_gaussians_derivative", "sample_gaussians_laplacian", "sample_gaussians_third_derivative",
-    "aggregate_neighbors", "plan_of", "count_pairs", "covariances_from_scales_rotations",
+    "aggregate_neighbors", "plan_of", "count_pairs", "covariances_from_scales_rotations", "sample_gaussians_jet",
 ]
 
 # ---------------------------------------------------------------------------------------
@@ -184,6 +184,65 @@ class _NativeOps:
                                                binning_buffer.data_ptr(), sample_binning_buffer.data_ptr(),
                                                ranges.data_ptr(), sample_ranges.data_ptr(), dmeans.data_ptr(),
                                                dvalues.data_ptr(), dconics.data_ptr(), st), "dgs_sample_backward")
+            if debug:
+                torch.cuda.synchronize(means.device)
+        return dmeans, dvalues, dconics
+
+    # -- value + derivative + Hessian in one traversal (not in the reference, whose callers make the
+    #    three calls of __init__.py:235-277 one after the other) ---------------------------
+    @staticmethod
+    def sample_gaussians_jet(means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
+                             sample_ranges, debug):
+        lib = _lib.load()
+        means = _f32c(means, "means"); values = _f32c(values, "values")
+        conics = _f32c(conics, "conics"); samples = _f32c(samples, "samples")
+        P, D = means.shape[0], means.shape[-1]
+        N, C = samples.shape[0], values.shape[-1]
+        shapes = [(N,) + (D,) * k + (C,) for k in range(3)]
+        if P == 0 or N == 0 or binning_buffer.numel() == 0:
+            return tuple(torch.zeros(sh, dtype=torch.float32, device=means.device) for sh in shapes)
+        plan = plan_of(binning_buffer, num_rendered)
+        if plan.P != P or plan.N != N or plan.D != D:
+            raise RuntimeError("binning buffers were built for different tensor shapes")
+        outs = tuple(torch.empty(sh, dtype=torch.float32, device=means.device) for sh in shapes)
+        with torch.cuda.device(means.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_sample_jet_forward(ctypes.byref(plan), C, means.data_ptr(), values.data_ptr(),
+                                                  conics.data_ptr(), samples.data_ptr(), binning_buffer.data_ptr(),
+                                                  sample_binning_buffer.data_ptr(), ranges.data_ptr(),
+                                                  sample_ranges.data_ptr(), outs[0].data_ptr(), outs[1].data_ptr(),
+                                                  outs[2].data_ptr(), st), "dgs_sample_jet_forward")
+            if debug:
+                torch.cuda.synchronize(means.device)
+        return outs
+
+    @staticmethod
+    def sample_gaussians_jet_backward(means, values, conics, samples, num_rendered, dL_dvalue, dL_dderivative, dL_dhessian,
+                                      binning_buffer, sample_binning_buffer, ranges, sample_ranges, debug):
+        """Any of the three incoming gradients may be None."""
+        lib = _lib.load()
+        means = _f32c(means, "means"); values = _f32c(values, "values")
+        conics = _f32c(conics, "conics"); samples = _f32c(samples, "samples")
+        douts = [None if g is None else _f32c(g, "dL_dout") for g in (dL_dvalue, dL_dderivative, dL_dhessian)]
+        P, D = means.shape[0], means.shape[-1]
+        N, C = samples.shape[0], values.shape[-1]
+        T = D * (D + 1) // 2
+        flat = torch.zeros(P * (D + C + T), dtype=torch.float32, device=means.device)
+        dmeans = flat[:P * D].view(P, D)
+        dvalues = flat[P * D:P * (D + C)].view(P, C)
+        dconics = flat[P * (D + C):].view(P, T)
+        if P == 0 or N == 0 or binning_buffer.numel() == 0 or all(g is None for g in douts):
+            return dmeans, dvalues, dconics
+        plan = plan_of(binning_buffer, num_rendered)
+        ptr = lambda g: None if g is None else g.data_ptr()
+        with torch.cuda.device(means.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.dgs_sample_jet_backward(ctypes.byref(plan), C, means.data_ptr(), values.data_ptr(),
+                                                   conics.data_ptr(), samples.data_ptr(), ptr(douts[0]), ptr(douts[1]),
+                                                   ptr(douts[2]), binning_buffer.data_ptr(),
+                                                   sample_binning_buffer.data_ptr(), ranges.data_ptr(),
+                                                   sample_ranges.data_ptr(), dmeans.data_ptr(), dvalues.data_ptr(),
+                                                   dconics.data_ptr(), st), "dgs_sample_jet_backward")
             if debug:
                 torch.cuda.synchronize(means.device)
         return dmeans, dvalues, dconics
@@ -420,6 +479,29 @@ class _SampleGaussiansThirdDerivative(torch.autograd.Function):
         return call_backward(ctx, _C.sample_gaussians_third_derivative_backward, grad_out, "3_bw")
 
 
+class _SampleGaussiansJet(torch.autograd.Function):
+    """(value, derivative, hessian) = the outputs of sample_gaussians, _derivative and _laplacian from ONE traversal;
+    one backward for whatever subset of the three the loss uses."""
+
+    @staticmethod
+    def forward(ctx, *args):
+        outs = call_forward(ctx, _C.sample_gaussians_jet, "jet_fw", *args)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, g_value, g_derivative, g_hessian):
+        means, values, conics, samples, binning_buffer, sample_binning_buffer, ranges, sample_ranges = ctx.saved_tensors
+        args = (means, values, conics, samples, ctx.num_rendered, g_value, g_derivative, g_hessian, binning_buffer,
+                sample_binning_buffer, ranges, sample_ranges, ctx.debug)
+        grad_means, grad_values, grad_conics = call_debug(_C.sample_gaussians_jet_backward, ctx.debug, "jet_bw", *args)
+        return (grad_means, grad_values, grad_conics, None, None, None, None, None, None, None)
+
+
+def sample_gaussians_jet(*args):
+    """Same 10 arguments as sample_gaussians; returns (value (N,C), derivative (N,D,C), hessian (N,D,D,C))."""
+    return _SampleGaussiansJet.apply(*args)
+
+
 class _AggregateNeighbors(torch.autograd.Function):
     @staticmethod
     def forward(ctx, features, transform, queries, keys, frequencies, distance_transform,
@@ -489,6 +571,10 @@ class GaussianSampler:
 
     def sample_gaussians_third_derivative(self):
         return sample_gaussians_third_derivative(*self._args())
+
+    def sample_gaussians_jet(self):
+        """(value, derivative, laplacian) of the three methods above from one traversal."""
+        return sample_gaussians_jet(*self._args())
 
     def preprocess_aggregate(self):
         # the reference overwrites self.ranges here (its __init__.py:298), which breaks a later

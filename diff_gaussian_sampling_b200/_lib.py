@@ -61,6 +61,10 @@ EXPORTS = {
                                           c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_sample_backward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
                                            c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dgs_sample_jet_forward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
+                                              c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dgs_sample_jet_backward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                               c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_microbench": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, ctypes.POINTER(ctypes.c_double), c_vp]),
     "dgs_count_pairs": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp]),
     "dgs_covariance_forward": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.c_int, c_vp, c_vp, c_vp]),

@@ -502,6 +502,35 @@ extern "C" __attribute__((visibility("default"))) int dgs_sample_backward(const 
                                (cudaStream_t)stream);
 }
 
+// value + derivative + Hessian in one traversal; see include/dgs_b200.h
+extern "C" __attribute__((visibility("default"))) int dgs_sample_jet_forward(const dgs_plan_t* plan, int C, const float* means_dev, const float* values_dev,
+                                      const float* conics_dev, const float* samples_dev, void* binning_dev,
+                                      const void* sample_binning_dev, const void* ranges_dev, const void* sample_ranges_dev,
+                                      float* out_value_dev, float* out_derivative_dev, float* out_hessian_dev, void* stream) {
+    (void)samples_dev; (void)sample_ranges_dev;
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    DGS_REQUIRE(C >= 1, DGS_ERR_BAD_ARG, "C must be >= 1");
+    DGS_REQUIRE(plan->N <= 0 || (out_value_dev && out_derivative_dev && out_hessian_dev), DGS_ERR_BAD_ARG, "all three outputs are required");
+    return dgs_launch_forward(plan, DGS_FN_JET, C, means_dev, values_dev, conics_dev, (uint8_t*)binning_dev,
+                              (const uint8_t*)sample_binning_dev, ranges_dev, out_value_dev, nullptr, (cudaStream_t)stream,
+                              out_derivative_dev, out_hessian_dev);
+}
+
+extern "C" __attribute__((visibility("default"))) int dgs_sample_jet_backward(const dgs_plan_t* plan, int C, const float* means_dev, const float* values_dev,
+                                       const float* conics_dev, const float* samples_dev, const float* dout_value_dev,
+                                       const float* dout_derivative_dev, const float* dout_hessian_dev, void* binning_dev,
+                                       const void* sample_binning_dev, const void* ranges_dev, const void* sample_ranges_dev,
+                                       float* dmeans_dev, float* dvalues_dev, float* dconics_dev, void* stream) {
+    (void)samples_dev; (void)sample_ranges_dev;
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    DGS_REQUIRE(C >= 1, DGS_ERR_BAD_ARG, "C must be >= 1");
+    return dgs_launch_backward(plan, DGS_FN_JET, C, means_dev, values_dev, conics_dev, dout_value_dev, (uint8_t*)binning_dev,
+                               (const uint8_t*)sample_binning_dev, ranges_dev, dmeans_dev, dvalues_dev, dconics_dev,
+                               (cudaStream_t)stream, dout_derivative_dev, dout_hessian_dev);
+}
+
 extern "C" __attribute__((visibility("default"))) int dgs_count_pairs(const dgs_plan_t* plan, int fn, const void* binning_dev, const void* sample_binning_dev,
                                unsigned long long* counter_dev, void* stream) {
     int rc = check_plan(plan);

@@ -45,6 +45,7 @@
 
 struct BwdArgs {
     const float* values; const float* conics; const float* dout;
+    const float* dout1; const float* dout2;       // jet: dL/dderivative, dL/dHessian (dout = dL/dvalue); any may be NULL
     const float* prec;
     const void* mask; int mask64;                 // survivor bitmasks of this function level
     const uint32_t* l1_start; const uint32_t* l1_ids;
@@ -59,7 +60,7 @@ template <int D, int FN, int CB>
 struct BwdCfg {
     static constexpr int T = D * (D + 1) / 2;
     static constexpr int U = dgs_nuniq(D, FN);
-    static constexpr int AFULL = dgs_ipow(D, FN);
+    static constexpr int AFULL = dgs_nfull(D, FN);
     static constexpr int SW0 = D + U * CB;                  // x | dOs[u][c]
     static constexpr int SW = (SW0 + 3) / 4 * 4;
     static constexpr int SAMP_FLOATS = 256 * SW < 2048 ? 256 * SW : 2048;
@@ -107,6 +108,19 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
 #pragma unroll
             for (int jx = i; jx < D; jx++) {
                 const float Wv = Wu[dgs_tri(D, i, jx)];
+                dSda[i] = fmaf(Wv, a[jx], dSda[i]);
+                dSda[jx] = fmaf(Wv, a[i], dSda[jx]);
+                dSdC[dgs_tri(D, i, jx)] -= Wv;
+            }
+    } else if (FN == DGS_FN_JET) {
+        // orders 0 + 1 + 2: the value part only enters through S
+#pragma unroll
+        for (int i = 0; i < D; i++) dSda[i] = Wu[1 + i];
+#pragma unroll
+        for (int i = 0; i < D; i++)
+#pragma unroll
+            for (int jx = i; jx < D; jx++) {
+                const float Wv = Wu[1 + D + dgs_tri(D, i, jx)];
                 dSda[i] = fmaf(Wv, a[jx], dSda[i]);
                 dSda[jx] = fmaf(Wv, a[i], dSda[jx]);
                 dSdC[dgs_tri(D, i, jx)] -= Wv;
@@ -354,11 +368,17 @@ __global__ void __launch_bounds__(BWD_THREADS, (D <= 2 && FN == 0 && CB == 1) ? 
                 for (int u = 0; u < U; u++)
 #pragma unroll
                     for (int c = 0; c < CB; c++) ds[u][c] = 0.f;
-                const float* dp = A.dout + (int64_t)sid * AFULL * A.C + A.ch0;
 #pragma unroll
-                for (int al = 0; al < AFULL; al++)
+                for (int al = 0; al < AFULL; al++) {
+                    const float* dp;
+                    if (FN != DGS_FN_JET) dp = A.dout + ((int64_t)sid * AFULL + al) * A.C;
+                    else if (al == 0) dp = A.dout ? A.dout + (int64_t)sid * A.C : nullptr;
+                    else if (al <= D) dp = A.dout1 ? A.dout1 + ((int64_t)sid * D + (al - 1)) * A.C : nullptr;
+                    else dp = A.dout2 ? A.dout2 + ((int64_t)sid * D * D + (al - 1 - D)) * A.C : nullptr;
+                    if (FN == DGS_FN_JET && dp == nullptr) continue;
 #pragma unroll
-                    for (int c = 0; c < CB; c++) ds[dgs_uniq_of(D, FN, al)][c] += dp[(int64_t)al * A.C + c];
+                    for (int c = 0; c < CB; c++) ds[dgs_uniq_of(D, FN, al)][c] += dp[A.ch0 + c];
+                }
 #pragma unroll
                 for (int u = 0; u < U; u++)
 #pragma unroll
@@ -483,6 +503,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_bwd_finalize_kernel(const flo
 }
 
 float dgs_tau_for(const dgs_plan_t* plan, int fn);
+int dgs_mask_level(int fn);
 int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st);
 
 template <int D, int FN>
@@ -510,20 +531,22 @@ static void bwd_launch_d(const BwdArgs& a, int fn, int n_coarse, int64_t P, cuda
             break;
         case 1: bwd_launch_fn<D, 1>(a, n_coarse, st); break;
         case 2: bwd_launch_fn<D, 2>(a, n_coarse, st); break;
-        default: bwd_launch_fn<D, 3>(a, n_coarse, st); break;
+        case 3: bwd_launch_fn<D, 3>(a, n_coarse, st); break;
+        default: bwd_launch_fn<D, DGS_FN_JET>(a, n_coarse, st); break;
     }
 }
 
 int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                         const float* conics, const float* dout, uint8_t* gbuf, const uint8_t* sbuf,
-                        const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st) {
+                        const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st,
+                        const float* dout_derivative, const float* dout_hessian) {
     (void)ranges;
     if (plan->N <= 0 || plan->n_coarse <= 0 || plan->P <= 0) return 0;
     BwdArgs a;
-    a.values = values; a.conics = conics; a.dout = dout;
+    a.values = values; a.conics = conics; a.dout = dout; a.dout1 = dout_derivative; a.dout2 = dout_hessian;
     a.prec = (const float*)(gbuf + plan->g_prec_off);
     a.mask64 = plan->mask_bytes == 8 ? 1 : 0;
-    a.mask = gbuf + plan->g_l1_mask_off + (size_t)(fn < 0 ? 0 : (fn > 3 ? 3 : fn)) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
+    a.mask = gbuf + plan->g_l1_mask_off + (size_t)dgs_mask_level(fn) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
     a.fine_start = (const uint32_t*)(sbuf + plan->s_fine_start_off);

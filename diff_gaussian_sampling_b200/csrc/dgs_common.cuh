@@ -88,10 +88,14 @@ int dgs_sort_pairs_u32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_
                        uint32_t* keys_alt, uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit, void* tmp,
                        cudaStream_t st);
 
+#define DGS_FN_JET 4   // function code of the fused value + derivative + Hessian traversal (dgs_field.cuh)
+
 // --- kernels launched from dgs_api.cu ---------------------------------------------------
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                        const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
-                       float* out, unsigned long long* pair_counter, cudaStream_t st);
+                       float* out, unsigned long long* pair_counter, cudaStream_t st,
+                       float* out_derivative = nullptr, float* out_hessian = nullptr);   // fn == DGS_FN_JET only
 int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                         const float* conics, const float* dout, uint8_t* gbuf, const uint8_t* sbuf,
-                        const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st);
+                        const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st,
+                        const float* dout_derivative = nullptr, const float* dout_hessian = nullptr);   // fn == DGS_FN_JET only

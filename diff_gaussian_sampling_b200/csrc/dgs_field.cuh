@@ -18,10 +18,14 @@
 DGS_HD constexpr int dgs_tri(int D, int i, int j) { return i * D - (i * (i - 1)) / 2 + (j - i); }
 DGS_HD constexpr int dgs_tri_sym(int D, int i, int j) { return i <= j ? dgs_tri(D, i, j) : dgs_tri(D, j, i); }
 // number of unique components of a symmetric order-n tensor in D dims
+// Function codes: 0..3 = the reference's gaussian / derivative / laplacian (full Hessian) / third; DGS_FN_JET = the
+// orders 0, 1 and 2 together in one traversal, components laid out value | gradient | Hessian.
 DGS_HD constexpr int dgs_nuniq(int D, int n) {
-    return n == 0 ? 1 : n == 1 ? D : n == 2 ? D * (D + 1) / 2 : D * (D + 1) * (D + 2) / 6;
+    return n == 0 ? 1 : n == 1 ? D : n == 2 ? D * (D + 1) / 2 : n == 3 ? D * (D + 1) * (D + 2) / 6 : 1 + D + D * (D + 1) / 2;
 }
 DGS_HD constexpr int dgs_ipow(int D, int n) { return n == 0 ? 1 : D * dgs_ipow(D, n - 1); }
+// number of full (non-unique) output components per sample and channel
+DGS_HD constexpr int dgs_nfull(int D, int n) { return n == DGS_FN_JET ? 1 + D + D * D : dgs_ipow(D, n); }
 // index of the sorted triple i<=j<=k in lexicographic enumeration (D <= 3); loop-free so that it folds to
 // a constant after unrolling (a loop here leaves the accumulator index dynamic -> local memory)
 DGS_HD constexpr int dgs_u3(int D, int i, int j, int k) {
@@ -42,6 +46,8 @@ DGS_HD constexpr int dgs_uniq_of(int D, int order, int alpha) {
     if (order == 0) return 0;
     if (order == 1) return alpha;
     if (order == 2) return dgs_tri_sym(D, alpha / D, alpha % D);
+    if (order == DGS_FN_JET)
+        return alpha == 0 ? 0 : (alpha <= D ? alpha : 1 + D + dgs_tri_sym(D, (alpha - 1 - D) / D, (alpha - 1 - D) % D));
     return dgs_u3_any(D, alpha / (D * D), (alpha / D) % D, alpha % D);
 }
 
@@ -124,6 +130,14 @@ struct DgsPair {
             for (int i = 0; i < D; i++)
 #pragma unroll
                 for (int j = i; j < D; j++) H[dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
+        } else if (FN == DGS_FN_JET) {
+            H[0] = 1.f;
+#pragma unroll
+            for (int i = 0; i < D; i++) H[1 + i] = a[i];
+#pragma unroll
+            for (int i = 0; i < D; i++)
+#pragma unroll
+                for (int j = i; j < D; j++) H[1 + D + dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
         } else {
             dgs_for_triples<D, 0, 0, 0>([&](auto ti, auto tj, auto tk) {
                 constexpr int i = decltype(ti)::value, j = decltype(tj)::value, k = decltype(tk)::value;
@@ -218,6 +232,14 @@ __device__ __forceinline__ void dgs_hermite(const float* a, const float* con, fl
         for (int i = 0; i < D; i++)
 #pragma unroll
             for (int j = i; j < D; j++) H[dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
+    } else if (FN == DGS_FN_JET) {
+        H[0] = 1.f;
+#pragma unroll
+        for (int i = 0; i < D; i++) H[1 + i] = a[i];
+#pragma unroll
+        for (int i = 0; i < D; i++)
+#pragma unroll
+            for (int j = i; j < D; j++) H[1 + D + dgs_tri(D, i, j)] = fmaf(a[i], a[j], -con[dgs_tri(D, i, j)]);
     } else {
         dgs_for_triples<D, 0, 0, 0>([&](auto ti, auto tj, auto tk) {
             constexpr int i = decltype(ti)::value, j = decltype(tj)::value, k = decltype(tk)::value;

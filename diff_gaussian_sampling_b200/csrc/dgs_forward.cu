@@ -42,6 +42,7 @@ struct FwdArgs {
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
     const float* fine_aabb; const float* coarse_aabb;
     float* out;
+    float* out1; float* out2;                     // jet: derivative (N, D, C) and Hessian (N, D, D, C); `out` is the value
     unsigned long long* pair_counter;
     int64_t N;
     int C, ch0, fpcD;
@@ -51,7 +52,7 @@ template <int D, int FN, int CB>
 struct FwdCfg {
     static constexpr int T = D * (D + 1) / 2;
     static constexpr int U = dgs_nuniq(D, FN);
-    static constexpr int AFULL = dgs_ipow(D, FN);
+    static constexpr int AFULL = dgs_nfull(D, FN);
     static constexpr int SMAX0 = 48 / (U * CB);
     static constexpr int SMAX = SMAX0 < 1 ? 1 : (SMAX0 > 8 ? 8 : SMAX0);   // samples per lane
     static constexpr int FW0 = D + T + (FN > 0 ? T : 0) + CB;              // mu | U | [conic] | v
@@ -341,11 +342,16 @@ __global__ void __launch_bounds__(FWD_THREADS, (D <= 2 && FN == 0 && CB == 1) ? 
                     const uint32_t j = pb + (uint32_t)i * 32 + lane;
                     if ((i < s_eff) && (j < pe)) {
                         const uint32_t sid = A.fine_ids[j];
-                        float* o = A.out + (int64_t)sid * AFULL * A.C + A.ch0;
 #pragma unroll
-                        for (int al = 0; al < AFULL; al++)
+                        for (int al = 0; al < AFULL; al++) {
+                            float* o;
+                            if (FN != DGS_FN_JET) o = A.out + ((int64_t)sid * AFULL + al) * A.C;
+                            else if (al == 0) o = A.out + (int64_t)sid * A.C;
+                            else if (al <= D) o = A.out1 + ((int64_t)sid * D + (al - 1)) * A.C;
+                            else o = A.out2 + ((int64_t)sid * D * D + (al - 1 - D)) * A.C;
 #pragma unroll
-                            for (int c = 0; c < CB; c++) o[(int64_t)al * A.C + c] = acc[i][dgs_uniq_of(D, FN, al)][c];
+                            for (int c = 0; c < CB; c++) o[A.ch0 + c] = acc[i][dgs_uniq_of(D, FN, al)][c];
+                        }
                     }
                 }
             }
@@ -358,6 +364,8 @@ __global__ void __launch_bounds__(FWD_THREADS, (D <= 2 && FN == 0 && CB == 1) ? 
 }
 
 float dgs_tau_for(const dgs_plan_t* plan, int fn) { return plan->tau + DGS_TAU_STEP * (float)fn; }
+// survivor-mask level of a function code: the jet uses the list of its highest order (levels are nested)
+int dgs_mask_level(int fn) { return fn == DGS_FN_JET ? 2 : (fn < 0 ? 0 : (fn > 3 ? 3 : fn)); }
 
 template <int D, int FN>
 static void fwd_launch_fn(FwdArgs a, int n_coarse, cudaStream_t st) {
@@ -378,7 +386,8 @@ static void fwd_launch_d(const FwdArgs& a, int fn, int n_coarse, cudaStream_t st
         case 0: fwd_launch_fn<D, 0>(a, n_coarse, st); break;
         case 1: fwd_launch_fn<D, 1>(a, n_coarse, st); break;
         case 2: fwd_launch_fn<D, 2>(a, n_coarse, st); break;
-        default: fwd_launch_fn<D, 3>(a, n_coarse, st); break;
+        case 3: fwd_launch_fn<D, 3>(a, n_coarse, st); break;
+        default: fwd_launch_fn<D, DGS_FN_JET>(a, n_coarse, st); break;
     }
 }
 
@@ -386,14 +395,15 @@ int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, f
 
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                        const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
-                       float* out, unsigned long long* pair_counter, cudaStream_t st) {
+                       float* out, unsigned long long* pair_counter, cudaStream_t st, float* out_derivative,
+                       float* out_hessian) {
     (void)ranges;
     if (plan->N <= 0 || plan->n_coarse <= 0) return 0;
     FwdArgs a;
     a.values = values; a.conics = conics;
     a.prec = (const float*)(gbuf + plan->g_prec_off);
     a.mask64 = plan->mask_bytes == 8 ? 1 : 0;
-    a.mask = gbuf + plan->g_l1_mask_off + (size_t)(fn < 0 ? 0 : (fn > 3 ? 3 : fn)) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
+    a.mask = gbuf + plan->g_l1_mask_off + (size_t)dgs_mask_level(fn) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
     a.fine_start = (const uint32_t*)(sbuf + plan->s_fine_start_off);
@@ -401,7 +411,7 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     a.fine_xyz = (const float*)(sbuf + plan->s_fine_xyz_off);
     a.fine_aabb = (const float*)(sbuf + plan->s_fine_aabb_off);
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
-    a.out = out; a.pair_counter = pair_counter;
+    a.out = out; a.out1 = out_derivative; a.out2 = out_hessian; a.pair_counter = pair_counter;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
     if (pair_counter) {
         DGS_NOTE_LAUNCHES(1);

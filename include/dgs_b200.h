@@ -198,6 +198,29 @@ int dgs_sample_backward(const dgs_plan_t* plan, int fn, int C,
                         const void* ranges_dev, const void* sample_ranges_dev,
                         float* dmeans_dev, float* dvalues_dev, float* dconics_dev, void* stream);
 
+/*
+ * Fused evaluation of the orders 0, 1 and 2 (value, derivative, full Hessian) in ONE traversal, and its backward
+ * (SURVEY.md §8 f-2).  Not in the reference: its callers run sample_gaussians, _derivative and _laplacian one after
+ * the other (__init__.py:235-289), i.e. three traversals and three backward passes over the same pairs.  The results
+ * equal those three calls (same formulas, forward.cu:168-243; all three use the pair list of the laplacian, which
+ * contains the other two).  out_value (N, C), out_derivative (N, D, C), out_hessian (N, D, D, C), all written in
+ * full.  Backward: any of the three dout pointers may be NULL (= zero gradient); dmeans/dvalues/dconics are
+ * overwritten with the gradient of the sum.  Asynchronous.
+ */
+int dgs_sample_jet_forward(const dgs_plan_t* plan, int C,
+                           const float* means_dev, const float* values_dev, const float* conics_dev,
+                           const float* samples_dev,
+                           void* binning_dev, const void* sample_binning_dev,
+                           const void* ranges_dev, const void* sample_ranges_dev,
+                           float* out_value_dev, float* out_derivative_dev, float* out_hessian_dev, void* stream);
+int dgs_sample_jet_backward(const dgs_plan_t* plan, int C,
+                            const float* means_dev, const float* values_dev, const float* conics_dev,
+                            const float* samples_dev,
+                            const float* dout_value_dev, const float* dout_derivative_dev, const float* dout_hessian_dev,
+                            void* binning_dev, const void* sample_binning_dev,
+                            const void* ranges_dev, const void* sample_ranges_dev,
+                            float* dmeans_dev, float* dvalues_dev, float* dconics_dev, void* stream);
+
 /* Pairs the forward/backward kernels evaluate for this plan (sum over fine tiles of
  * samples x surviving Gaussians); debugging / roofline accounting.  counter_dev: one
  * zero-filled uint64 on the device.  Asynchronous. */

@@ -30,7 +30,7 @@ def main():
     tm, tv, tcov, tcon, ts = (torch.from_numpy(x).to(dev) for x in (m, v, cov, con, s))
     N = s.shape[0]
     calls = [dgs.sample_gaussians, dgs.sample_gaussians_derivative, dgs.sample_gaussians_laplacian,
-             dgs.sample_gaussians_third_derivative]
+             dgs.sample_gaussians_third_derivative, dgs.sample_gaussians_jet]   # fn 4: value + derivative + Hessian fused
     for rep in range(4):
         torch.cuda.synchronize()
         e0 = ev()
@@ -41,9 +41,10 @@ def main():
         e2 = ev()
         o = calls[fn](mm, vv, cc, ts, nr, gb, sb, rg, srg, False)
         e3 = ev()
-        g = torch.randn_like(o)
+        o = o if isinstance(o, tuple) else (o,)
+        g = tuple(torch.randn_like(x) for x in o)
         e4 = ev()
-        o.backward(g)
+        torch.autograd.backward(o, g)
         e5 = ev()
         torch.cuda.synchronize()
         plan = dgs.plan_of(gb, nr)
