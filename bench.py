@@ -75,50 +75,74 @@ def make_inputs(workload, rank, world):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md's clocks line).  NVML in-process,
+    every 5 ms from a thread (the timed region is tens of milliseconds: an `nvidia-smi -lms` child process has not
+    printed its first line by then); `nvidia-smi` once as a fallback when NVML cannot be loaded."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.sm, self.reasons, self.mx = index, [], set(), None
+        self.stop_flag, self.thread, self.nvml, self.handle = threading.Event(), None, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:  # noqa: BLE001
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self._sample()
+            self.thread = threading.Thread(target=self._loop, daemon=True)
             self.thread.start()
         except Exception:  # noqa: BLE001
-            self.proc = None
+            self.nvml = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+    def _sample(self):
+        n = self.nvml
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        try:
+            bits = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+        except Exception:  # noqa: BLE001
+            bits = 0
+        for bit, name in self.REASONS.items():
+            if bits & bit:
+                self.reasons.add(name)
+
+    def _loop(self):
+        while not self.stop_flag.wait(0.005):
+            try:
+                self._sample()
+            except Exception:  # noqa: BLE001
+                return
+
+    def _smi_once(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=20).stdout.strip().splitlines()[0]
+            f = [x.strip() for x in out.split(",")]
+            names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+            return {"sm_mhz": float(f[0]), "sm_max_mhz": float(f[1]),
+                    "reasons": sorted(nm for nm, v in zip(names, f[2:6]) if v.lower().startswith("active")),
+                    "samples": 1, "source": "nvidia-smi"}
+        except Exception:  # noqa: BLE001
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml and nvidia-smi unavailable"], "samples": 0}
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:  # noqa: BLE001
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if val.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.nvml is None:
+            return self._smi_once()
+        self.stop_flag.set()
+        if self.thread:
+            self.thread.join(timeout=1)
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.mx,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml"}
 
 
 # ---------------------------------------------------------------------------------------
@@ -243,34 +267,33 @@ def run_ours(args, rank, world, local_rank):
         del gs
     except Exception:  # noqa: BLE001
         t_pre_reuse = []
-    # ---- end to end: pinned host inputs -> H2D every step, gradients + loss -> D2H every step ----
+    # ---- end to end: pinned host inputs -> H2D every step, gradients + loss -> D2H every step, through the package's
+    #      HostPipeline (double-buffered: the copy of step i+1's inputs overlaps step i; every step's bytes cross the
+    #      bus inside the timed region, which brackets all K steps; no L2 flush here: 170 MB of fresh inputs per step
+    #      and a working set of several hundred MB exceed the 126 MB L2) ----
     e2e = None
     if not args.no_e2e:
+        from diff_gaussian_sampling_b200.host_pipeline import HostPipeline
         grads_host = torch.empty(P * (D + C + T), dtype=torch.float32).pin_memory()
         loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+        pipe = HostPipeline(dev)
 
-        def e2e_step():
-            t = {k: v.to(dev, non_blocking=True) for k, v in pinned.items()}
+        def e2e_step(t):
             flat, out = step(t)
-            grads_host.copy_(flat, non_blocking=True)
-            loss_host.copy_((out * dout).sum().reshape(1), non_blocking=True)
+            return flat, (out * dout).sum().reshape(1)
 
-        for _ in range(2):
-            e2e_step()
+        def e2e_run(k):
+            return pipe.run((pinned for _ in range(k)), e2e_step, lambda i: (grads_host, loss_host))
+
+        e2e_run(3)
         barrier()
-        e2e_ms = 0.0
-        for _ in range(args.steps):
-            l2_flush.zero_()
-            barrier()
-            a, b = ev(), ev()
-            a.record()
-            e2e_step()
-            b.record()
-            barrier()
-            e2e_ms += a.elapsed_time(b)
-        h2d = sum(v.numel() * v.element_size() for v in pinned.values())
-        d2h = grads_host.numel() * 4 + 4
-        e2e = dict(ms=e2e_ms, h2d=h2d, d2h=d2h)
+        pipe.h2d_bytes = pipe.d2h_bytes = 0
+        a, b = ev(), ev()
+        a.record()
+        k = e2e_run(args.steps)
+        b.record()
+        barrier()
+        e2e = dict(ms=a.elapsed_time(b), h2d=pipe.h2d_bytes // k, d2h=pipe.d2h_bytes // k, loss=float(loss_host[0]))
     clk = clocks.stop()
     return dict(tot_ms=tot_ms, t_pre=t_pre, t_fwd=t_fwd, t_bwd=t_bwd, e2e=e2e, t_pre_reuse=t_pre_reuse, clocks=clk, launches=launches,
                 N=N, P=P, D=D, C=C, fn=fn, state=state, dgs=dgs, lib=lib, _lib=_lib, bounds=bounds, host=host)
@@ -444,7 +467,9 @@ def main():
         }
         if r["e2e"]:
             line["e2e"] = {"value": N * world * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": r["e2e"]["h2d"],
-                           "d2h_bytes_per_step": r["e2e"]["d2h"], "ms_per_step": e2e_ms / K}
+                           "d2h_bytes_per_step": r["e2e"]["d2h"], "ms_per_step": e2e_ms / K,
+                           "staging": "HostPipeline depth 2: H2D of step i+1 overlaps step i; K steps timed as one region, "
+                                      "pipeline fill included"}
         if not args.no_cpu_baseline and world == 1:   # reported at N=1 only
             try:
                 line["cpu_baseline"] = cpu_port_baseline(args.workload, 16 if P >= 1_000_000 else 32)

@@ -36,6 +36,9 @@
 #ifndef BWD_TUNED
 #define BWD_TUNED 7   // CTAs per SM of the 2D single-channel gaussian kernel (measured: 7 beats 8, 9, 10; profiles/r01_sweep_occupancy.jsonl)
 #endif
+#ifndef BWD_NG_HI
+#define BWD_NG_HI 1   // Gaussians per lane for the derivative orders and the jet (D <= 2); 2 measured within 4 % (profiles/r01_exp_mask_branchfree_ng2.jsonl)
+#endif
 #define BWD_WARPS 4
 #define BWD_THREADS (BWD_WARPS * 32)
 #define BWD_QF 96    // fast-id queue slots per warp
@@ -65,7 +68,7 @@ struct BwdCfg {
     static constexpr int SW = (SW0 + 3) / 4 * 4;
     static constexpr int SAMP_FLOATS = 256 * SW < 2048 ? 256 * SW : 2048;
     static constexpr int SCAP = SAMP_FLOATS / SW;           // samples per pass
-    static constexpr int G = FN == 0 ? 2 : 1;               // Gaussians per lane on the fast path
+    static constexpr int G = FN == 0 ? 2 : (D <= 2 ? BWD_NG_HI : 1);   // Gaussians per lane on the fast path
     static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG + BWD_QRAW;
 };
 
