@@ -36,6 +36,9 @@
 #ifndef BWD_TUNED
 #define BWD_TUNED 7   // CTAs per SM of the 2D single-channel gaussian kernel (measured: 7 beats 8, 9, 10; profiles/r01_sweep_occupancy.jsonl)
 #endif
+#ifndef BWD_TUNED_3D
+#define BWD_TUNED_3D 0   // same for D == 3 (0 = ptxas' choice, 95 registers; 4, 6, 7 measured no better)
+#endif
 #ifndef BWD_NG_HI
 #define BWD_NG_HI 1   // Gaussians per lane for the derivative orders and the jet (D <= 2); 2 measured within 4 % (profiles/r01_exp_mask_branchfree_ng2.jsonl)
 #endif
@@ -325,7 +328,7 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
 }
 
 template <int D, int FN, int CB, bool VPOST>
-__global__ void __launch_bounds__(BWD_THREADS, (D <= 2 && FN == 0 && CB == 1) ? BWD_TUNED : BWD_MINB) dgs_backward_kernel(const BwdArgs A) {
+__global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? BWD_TUNED : BWD_TUNED_3D) : BWD_MINB) dgs_backward_kernel(const BwdArgs A) {
     using K = BwdCfg<D, FN, CB>;
     constexpr int U = K::U, AFULL = K::AFULL, SW = K::SW, SW0 = K::SW0, SCAP = K::SCAP, NG = K::G;
     constexpr int PW = DGS_PREC_W(D);

@@ -28,6 +28,9 @@
 #ifndef FWD_TUNED
 #define FWD_TUNED 6   // CTAs per SM of the 2D single-channel gaussian kernel (measured: 6 beats 5 and 8)
 #endif
+#ifndef FWD_TUNED_3D
+#define FWD_TUNED_3D 6   // same for D == 3 (measured: 6 -> 8.39 ms on cfg3, ptxas' own choice 8.72, 4 -> 9.54; profiles/r01_sweep_occupancy_3d.jsonl)
+#endif
 #define FWD_WARPS 4
 #define FWD_THREADS (FWD_WARPS * 32)
 #define FWD_CAPF 64   // staged fast records per warp (flushed when more than CAPF-32 are waiting)
@@ -181,7 +184,7 @@ __device__ __forceinline__ void fwd_eval_general(const float* __restrict__ sG, i
 }
 
 template <int D, int FN, int CB, bool COUNT_ONLY>
-__global__ void __launch_bounds__(FWD_THREADS, (D <= 2 && FN == 0 && CB == 1) ? FWD_TUNED : FWD_MINB) dgs_forward_kernel(const FwdArgs A) {
+__global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? FWD_TUNED : FWD_TUNED_3D) : FWD_MINB) dgs_forward_kernel(const FwdArgs A) {
     using K = FwdCfg<D, FN, CB>;
     constexpr int T = K::T, U = K::U, AFULL = K::AFULL, SMAX = K::SMAX, FW = K::FW, GW = K::GW, GW0 = K::GW0;
     constexpr int PW = DGS_PREC_W(D);
