@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--fn", type=int, default=0, help="0 gaussian, 1 derivative, 2 laplacian, 3 third")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-per-function", action="store_true", help="skip the informational derivative/laplacian/third/jet timings")
     return ap.parse_args()
 
 
@@ -267,6 +268,44 @@ def run_ours(args, rank, world, local_rank):
         del gs
     except Exception:  # noqa: BLE001
         t_pre_reuse = []
+    # ---- informational: forward / backward of the other functions and of the fused jet on the same
+    #      binning, 2 repetitions each, best of; not part of `value` ----
+    per_fn = {}
+    if world == 1 and fn == 0 and not args.no_per_function:
+        try:
+            nr, gb, sb, rg, srg, _ = dgs._C.preprocess_gaussians(devt["means"], devt["values"], devt["covariances"],
+                                                               devt["conics"], devt["samples"], False, bounds=bounds)
+            a5 = (devt["means"], devt["values"], devt["conics"], devt["samples"], nr)
+            for name, order in (("derivative", 1), ("laplacian", 2), ("third", 3)):
+                g = torch.randn((N,) + (D,) * order + (C,), device=dev, generator=gen)
+                best = [1e30, 1e30]
+                for _ in range(2):
+                    l2_flush.zero_()
+                    e = [ev() for _ in range(3)]
+                    e[0].record()
+                    calls[order](*a5, gb, sb, rg, srg, False)
+                    e[1].record()
+                    bcalls[order](*a5, g, gb, sb, rg, srg, False)
+                    e[2].record(); torch.cuda.synchronize()
+                    best = [min(best[0], e[0].elapsed_time(e[1])), min(best[1], e[1].elapsed_time(e[2]))]
+                per_fn[name] = {"forward": best[0], "backward": best[1]}
+                del g
+            gs3 = [torch.randn((N,) + (D,) * k + (C,), device=dev, generator=gen) for k in range(3)]
+            best = [1e30, 1e30]
+            for _ in range(2):
+                l2_flush.zero_()
+                e = [ev() for _ in range(3)]
+                e[0].record()
+                dgs._C.sample_gaussians_jet(*a5, gb, sb, rg, srg, False)
+                e[1].record()
+                dgs._C.sample_gaussians_jet_backward(*a5, gs3[0], gs3[1], gs3[2], gb, sb, rg, srg, False)
+                e[2].record(); torch.cuda.synchronize()
+                best = [min(best[0], e[0].elapsed_time(e[1])), min(best[1], e[1].elapsed_time(e[2]))]
+            per_fn["jet_value_derivative_laplacian_fused"] = {"forward": best[0], "backward": best[1]}
+            del gs3
+            torch.cuda.empty_cache()
+        except Exception as ex:  # noqa: BLE001
+            per_fn["error"] = repr(ex)[:200]
     # ---- end to end: pinned host inputs -> H2D every step, gradients + loss -> D2H every step, through the package's
     #      HostPipeline (double-buffered: the copy of step i+1's inputs overlaps step i; every step's bytes cross the
     #      bus inside the timed region, which brackets all K steps; no L2 flush here: 170 MB of fresh inputs per step
@@ -295,7 +334,7 @@ def run_ours(args, rank, world, local_rank):
         barrier()
         e2e = dict(ms=a.elapsed_time(b), h2d=pipe.h2d_bytes // k, d2h=pipe.d2h_bytes // k, loss=float(loss_host[0]))
     clk = clocks.stop()
-    return dict(tot_ms=tot_ms, t_pre=t_pre, t_fwd=t_fwd, t_bwd=t_bwd, e2e=e2e, t_pre_reuse=t_pre_reuse, clocks=clk, launches=launches,
+    return dict(tot_ms=tot_ms, t_pre=t_pre, t_fwd=t_fwd, t_bwd=t_bwd, e2e=e2e, t_pre_reuse=t_pre_reuse, per_fn=per_fn, clocks=clk, launches=launches,
                 N=N, P=P, D=D, C=C, fn=fn, state=state, dgs=dgs, lib=lib, _lib=_lib, bounds=bounds, host=host)
 
 
@@ -444,6 +483,7 @@ def main():
             "breakdown_ms": {"preprocess": pre_ms, "forward": fwd_ms, "backward": bwd_ms,
                              "preprocess_with_fixed_points_reusing_sample_binning":
                                  (med(r["t_pre_reuse"][1:]) if len(r["t_pre_reuse"]) > 1 else None)},
+            "per_function_ms": r["per_fn"] or None,
             "fwd_bwd_only_points_per_s": N / ((fwd_ms + bwd_ms) * 1e-3),
             "pairs_evaluated_per_pass": pairs, "pairs_per_point": pairs / N,
             "gpu_launches": int(r["launches"]),
