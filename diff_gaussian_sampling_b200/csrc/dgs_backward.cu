@@ -39,6 +39,9 @@
 #ifndef BWD_TUNED_3D
 #define BWD_TUNED_3D 0   // same for D == 3 (0 = ptxas' choice, 95 registers; 4, 6, 7 measured no better)
 #endif
+#ifndef BWD_MOMENTS
+#define BWD_MOMENTS 1   // derivative orders, one channel: accumulate C- and v-free moments (bwd_pair_moments)
+#endif
 #ifndef BWD_NG_HI
 #define BWD_NG_HI 1   // Gaussians per lane for the derivative orders and the jet (D <= 2); 2 measured within 4 % (profiles/r01_exp_mask_branchfree_ng2.jsonl)
 #endif
@@ -75,32 +78,11 @@ struct BwdCfg {
     static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG + BWD_QRAW;
 };
 
-// per-pair VJP for FN >= 1: accumulates dV[c], dM[m], dC[k] (already multiplied by G)
-template <int D, int FN, int CB>
-__device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G, const float* con, const float* val,
-                                         const float* dOs, float* dV, float* dM, float* dC) {
+// Phi = sum_u W_u H_u(a, C): its partial derivatives with respect to a (dSda) and the EXPLICIT ones with respect to the
+// packed conic (dSdC); the dependence through a = C X is handled by the callers.
+template <int D, int FN>
+__device__ __forceinline__ void bwd_phi_grads(const float* a, const float* con, const float* Wu, float* dSda, float* dSdC) {
     constexpr int T = D * (D + 1) / 2;
-    constexpr int U = dgs_nuniq(D, FN);
-    float H[U];
-    dgs_hermite<D, FN>(a, con, H);
-    // hd_c = sum_u H_u dOs[u][c];  W_u = sum_c v_c dOs[u][c];  S = sum_c v_c hd_c
-    float S = 0.f;
-    float Wu[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) Wu[u] = 0.f;
-#pragma unroll
-    for (int c = 0; c < CB; c++) {
-        float hd = 0.f;
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            const float d_ = dOs[u * CB + c];
-            hd = fmaf(H[u], d_, hd);
-            Wu[u] = fmaf(val[c], d_, Wu[u]);
-        }
-        dV[c] = fmaf(G, hd, dV[c]);
-        S = fmaf(val[c], hd, S);
-    }
-    float dSda[D], dSdC[T];
 #pragma unroll
     for (int d = 0; d < D; d++) dSda[d] = 0.f;
 #pragma unroll
@@ -144,6 +126,73 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
                     dSdC[dgs_tri(D, jx, k)] = fmaf(Wv, a[i], dSdC[dgs_tri(D, jx, k)]);
         });
     }
+}
+
+// Single-channel form of the same VJP with the per-Gaussian factors pulled out of the pair loop (the way fn 0 keeps raw
+// moments).  With Phi = sum_u dO_u H_u(a, C), a = C X:
+//   dL/dv   =     sum_s G Phi
+//   dL/dmu  = v C sum_s G (dPhi/da - Phi X)                                      -> A1, C and v applied once per batch
+//   dL/dC_mn= v   sum_s [ B_m X_n (+ B_n X_m) + G dPhi/dC_mn|explicit ],  B = G (dPhi/da - Phi X / 2)
+// which saves the D x D product with C and about half of the conic arithmetic per pair.
+template <int D, int FN>
+__device__ __forceinline__ void bwd_pair_moments(const float* X, const float* a, float G, const float* con, const float* dOs,
+                                                 float& dV, float* A1, float* dC) {
+    constexpr int T = D * (D + 1) / 2;
+    constexpr int U = dgs_nuniq(D, FN);
+    float H[U];
+    dgs_hermite<D, FN>(a, con, H);
+    float Phi = 0.f;
+#pragma unroll
+    for (int u = 0; u < U; u++) Phi = fmaf(H[u], dOs[u], Phi);
+    float dPda[D], dPdC[T];
+    bwd_phi_grads<D, FN>(a, con, dOs, dPda, dPdC);
+    const float GP = G * Phi, hGP = 0.5f * GP;
+    dV += GP;
+    float B[D];
+#pragma unroll
+    for (int m = 0; m < D; m++) {
+        const float Gd = G * dPda[m];
+        A1[m] += fmaf(-GP, X[m], Gd);
+        B[m] = fmaf(-hGP, X[m], Gd);
+    }
+#pragma unroll
+    for (int m = 0; m < D; m++)
+#pragma unroll
+        for (int n = m; n < D; n++) {
+            float c = fmaf(B[m], X[n], dC[dgs_tri(D, m, n)]);
+            if (m != n) c = fmaf(B[n], X[m], c);
+            if (FN != 1) c = fmaf(G, dPdC[dgs_tri(D, m, n)], c);   // the derivative has no explicit conic term
+            dC[dgs_tri(D, m, n)] = c;
+        }
+}
+
+// per-pair VJP for FN >= 1: accumulates dV[c], dM[m], dC[k] (already multiplied by G)
+template <int D, int FN, int CB>
+__device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G, const float* con, const float* val,
+                                         const float* dOs, float* dV, float* dM, float* dC) {
+    constexpr int T = D * (D + 1) / 2;
+    constexpr int U = dgs_nuniq(D, FN);
+    float H[U];
+    dgs_hermite<D, FN>(a, con, H);
+    // hd_c = sum_u H_u dOs[u][c];  W_u = sum_c v_c dOs[u][c];  S = sum_c v_c hd_c
+    float S = 0.f;
+    float Wu[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) Wu[u] = 0.f;
+#pragma unroll
+    for (int c = 0; c < CB; c++) {
+        float hd = 0.f;
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const float d_ = dOs[u * CB + c];
+            hd = fmaf(H[u], d_, hd);
+            Wu[u] = fmaf(val[c], d_, Wu[u]);
+        }
+        dV[c] = fmaf(G, hd, dV[c]);
+        S = fmaf(val[c], hd, S);
+    }
+    float dSda[D], dSdC[T];
+    bwd_phi_grads<D, FN>(a, con, Wu, dSda, dSdC);
 #pragma unroll
     for (int m = 0; m < D; m++) {
         float g = -a[m] * S;
@@ -180,6 +229,9 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
     using K = BwdCfg<D, FN, CB>;
     constexpr int T = K::T, U = K::U, SW = K::SW, SW0 = K::SW0;
     constexpr int PW = DGS_PREC_W(D);
+    // single channel, derivative orders: per-Gaussian factors are applied after the loop (bwd_pair_moments); D == 1 `third`
+    // keeps the literal reference expression of bwd_pair
+    constexpr bool MOMENTS = BWD_MOMENTS && FN > 0 && CB == 1 && !(D == 1 && FN == 3);
     uint32_t id[NG];
     bool valid[NG], exact[NG];
     float mu[NG][D], geo[NG][T], con[NG][T], val[NG][CB];
@@ -308,12 +360,25 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
                 for (int i = 0; i < D; i++)
 #pragma unroll
                     for (int j = i; j < D; j++) dC[g][dgs_tri(D, i, j)] = fmaf(wX[i], X[j], dC[g][dgs_tri(D, i, j)]);
+            } else if constexpr (MOMENTS) {
+                bwd_pair_moments<D, FN>(X, a, Gv, con[g], sr + D, dV[g][0], dM[g], dC[g]);
             } else {
                 bwd_pair<D, FN, CB>(X, a, Gv, con[g], val[g], sr + D, dV[g], dM[g], dC[g]);
             }
         }
     }
     }   // scalar path
+    if constexpr (MOMENTS) {
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            float t[D];
+            dgs_conic_times<D>(con[g], dM[g], t);
+#pragma unroll
+            for (int d = 0; d < D; d++) dM[g][d] = val[g][0] * t[d];
+#pragma unroll
+            for (int k = 0; k < T; k++) dC[g][k] *= val[g][0];
+        }
+    }
 #pragma unroll
     for (int g = 0; g < NG; g++) {
         if (valid[g]) {
