@@ -319,8 +319,12 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
             if (FAST) {
 #pragma unroll
                 for (int d = 0; d < D; d++) X[d] = mu[g][d] - sr[d];
-                Gv = dgs_white_G<D>(X, geo[g]);
-                if (FN > 0) dgs_conic_times<D>(con[g], X, a);
+                if (FN == 0) {
+                    Gv = dgs_white_G<D>(X, geo[g]);
+                } else {
+                    dgs_conic_times<D>(con[g], X, a);
+                    Gv = dgs_G_from_a<D>(X, a);
+                }
             } else {
                 if (exact[g]) {
                     DgsPair<D, FN, true, true> p;

@@ -185,6 +185,17 @@ __device__ __forceinline__ float dgs_white_G(const float* X, const float* U) {
     return dgs_ex2(np);
 }
 
+// The derivative orders need a = C X anyway; there G comes from it directly, exp(-X.a / 2) = 2^(-(log2(e)/2) X.a),
+// in D + 1 operations instead of the D(D+1)/2 + D of the whitened form (and the record needs no Cholesky factor).
+#define DGS_NHALF_LOG2E (-0.72134752044448170368f)
+template <int D>
+__device__ __forceinline__ float dgs_G_from_a(const float* X, const float* a) {
+    float q = X[0] * a[0];
+#pragma unroll
+    for (int d = 1; d < D; d++) q = fmaf(X[d], a[d], q);
+    return dgs_ex2(q * DGS_NHALF_LOG2E);
+}
+
 // Packed (two-lane) form of the same: |U X|^2 for two pairs at once with FFMA2/FMUL2 (sm_100 packed FP32: one issue
 // slot, two fp32 results, each rounded exactly like the scalar instruction).  The accumulation kernels are bound by
 // issue slots and by the FMA pipe, not by flops alone; packing two samples (forward) or two Gaussians (backward) halves

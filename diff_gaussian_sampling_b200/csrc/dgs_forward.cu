@@ -58,7 +58,7 @@ struct FwdCfg {
     static constexpr int AFULL = dgs_nfull(D, FN);
     static constexpr int SMAX0 = 48 / (U * CB);
     static constexpr int SMAX = SMAX0 < 1 ? 1 : (SMAX0 > 8 ? 8 : SMAX0);   // samples per lane
-    static constexpr int FW0 = D + T + (FN > 0 ? T : 0) + CB;              // mu | U | [conic] | v
+    static constexpr int FW0 = D + T + CB;                                 // mu | U (fn 0) or conic (fn > 0) | v
     static constexpr int FW = (FW0 + 1) / 2 * 2;
     static constexpr int GW0 = D + T + CB + 1;                             // mu | conic | v | exact flag
     static constexpr int GW = (GW0 + 1) / 2 * 2;
@@ -118,20 +118,21 @@ __device__ __forceinline__ void fwd_eval_fast(const float* __restrict__ sF, int 
             const float2 v = *(const float2*)(sF + k * FW + q * 2);
             r[q * 2] = v.x; r[q * 2 + 1] = v.y;
         }
-        const float* val = r + D + T + (FN > 0 ? T : 0);
+        const float* val = r + D + T;
 #pragma unroll
         for (int i = 0; i < S; i++) {
             float X[D];
 #pragma unroll
             for (int d = 0; d < D; d++) X[d] = r[d] - x[i][d];
-            const float G = dgs_white_G<D>(X, r + D);
             if (FN == 0) {
+                const float G = dgs_white_G<D>(X, r + D);
 #pragma unroll
                 for (int c = 0; c < CB; c++) acc[i][0][c] = fmaf(val[c], G, acc[i][0][c]);
             } else {
                 float a[D], H[U];
-                dgs_conic_times<D>(r + D + T, X, a);
-                dgs_hermite<D, FN>(a, r + D + T, H);
+                dgs_conic_times<D>(r + D, X, a);
+                const float G = dgs_G_from_a<D>(X, a);
+                dgs_hermite<D, FN>(a, r + D, H);
 #pragma unroll
                 for (int c = 0; c < CB; c++) {
                     const float vg = val[c] * G;
@@ -287,13 +288,13 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         if (fast) {
                             float* r = sF + (nf + __popc(balF & lt)) * FW;
 #pragma unroll
-                            for (int q = 0; q < D + T; q++) r[q] = pr[q];
+                            for (int q = 0; q < D + (FN == 0 ? T : 0); q++) r[q] = pr[q];
                             if (FN > 0) {
 #pragma unroll
-                                for (int k = 0; k < T; k++) r[D + T + k] = A.conics[(int64_t)id * T + k];
+                                for (int k = 0; k < T; k++) r[D + k] = A.conics[(int64_t)id * T + k];
                             }
 #pragma unroll
-                            for (int c = 0; c < CB; c++) r[D + T + (FN > 0 ? T : 0) + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
+                            for (int c = 0; c < CB; c++) r[D + T + c] = A.values[(int64_t)id * A.C + A.ch0 + c];
                         } else {
                             float* r = sG + (ng + __popc(balG & lt)) * GW;
 #pragma unroll
