@@ -158,6 +158,51 @@ static void gauss_layout(dgs_plan_t* pl) {
 // ---------------------------------------------------------------------------------------
 // step 1: bounds, grid, cull records, tile hierarchy
 // ---------------------------------------------------------------------------------------
+// ---------------------------------------------------------------------------------------
+// Reading the device header back.  A cudaMemcpy D2H would queue on the device-to-host copy engine behind whatever
+// the caller has in flight there (e.g. the previous step's 24 MB of gradients draining to the host: +0.45 ms per
+// sync, measured with HostPipeline); a one-warp kernel writing the 96-byte header into mapped pinned host memory
+// depends on nothing but the stream.  One pinned slot per host thread, allocated on first use and kept.
+// ---------------------------------------------------------------------------------------
+__global__ void dgs_header_to_host_kernel(const DgsDevHeader* __restrict__ src, volatile uint32_t* dst) {
+    const uint32_t* s = (const uint32_t*)src;
+    for (int i = threadIdx.x; i < (int)(sizeof(DgsDevHeader) / 4); i += 32) dst[i] = s[i];
+    __threadfence_system();
+}
+
+// Small host -> device writes go through kernel arguments for the same reason: a cudaMemcpy H2D from pageable memory
+// would wait on the host-to-device copy engine behind the caller's own prefetch of the next batch.
+struct DgsBounds6 { float v[6]; };
+__global__ void dgs_set_bounds_kernel(DgsDevHeader* h, DgsBounds6 b, int D) {
+    if (threadIdx.x < D) { h->lo[threadIdx.x] = b.v[threadIdx.x]; h->hi[threadIdx.x] = b.v[D + threadIdx.x]; }
+}
+__global__ void dgs_store_plan_kernel(uint32_t* dst0, uint32_t* dst1, dgs_plan_t plan) {
+    const uint32_t* s = (const uint32_t*)&plan;
+    for (int i = threadIdx.x; i < (int)(sizeof(dgs_plan_t) / 4); i += blockDim.x) { dst0[i] = s[i]; dst1[i] = s[i]; }
+}
+
+static int read_header(const DgsDevHeader* hdr_dev, DgsDevHeader* out, cudaStream_t st) {
+    static thread_local DgsDevHeader* slot = nullptr;
+    static thread_local bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, sizeof(DgsDevHeader), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) slot = (DgsDevHeader*)p;
+        else (void)cudaGetLastError();
+    }
+    if (slot) {
+        dgs_header_to_host_kernel<<<1, 32, 0, st>>>(hdr_dev, (volatile uint32_t*)slot);
+        DGS_NOTE_LAUNCHES(1);
+        DGS_LAUNCH_CHECK();
+        DGS_CUDA(cudaStreamSynchronize(st));
+        memcpy(out, slot, sizeof(*out));
+        return 0;
+    }
+    DGS_CUDA(cudaMemcpyAsync(out, hdr_dev, sizeof(*out), cudaMemcpyDeviceToHost, st));
+    DGS_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
 static int choose_tiles(dgs_plan_t* pl) {
     const int D = pl->D;
     // samples per OCCUPIED cell: a point shard spans only part of the (global) bounding box
@@ -239,8 +284,11 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
     int rc = dgs_launch_header_init(hdr, st);
     if (rc) return rc;
     if (bounds_host) {
-        DGS_CUDA(cudaMemcpyAsync(hdr->lo, bounds_host, sizeof(float) * D, cudaMemcpyHostToDevice, st));
-        DGS_CUDA(cudaMemcpyAsync(hdr->hi, bounds_host + D, sizeof(float) * D, cudaMemcpyHostToDevice, st));
+        DgsBounds6 b6;
+        for (int d = 0; d < 2 * D; d++) b6.v[d] = bounds_host[d];
+        dgs_set_bounds_kernel<<<1, 32, 0, st>>>(hdr, b6, D);
+        DGS_NOTE_LAUNCHES(1);
+        DGS_LAUNCH_CHECK();
         // the extent of THIS call's samples (a rank's shard) still sizes the tiles: reduce it, but keep the given bounds
         rc = dgs_launch_bounds(samples_dev, N, D, hdr, false, st);
         if (rc) return rc;
@@ -252,8 +300,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
                          (float*)(g + gl.crecR), st);
     if (rc) return rc;
     DgsDevHeader h;
-    DGS_CUDA(cudaMemcpyAsync(&h, hdr, sizeof(h), cudaMemcpyDeviceToHost, st));
-    DGS_CUDA(cudaStreamSynchronize(st));
+    rc = read_header(hdr, &h, st);
+    if (rc) return rc;
     // tile_grid = ceil((max - min + 1e-6f) / 0.51f)   (sample_points.cu:72-73; ATen divides a CUDA
     // tensor by a CPU scalar by multiplying with the fp32 reciprocal)
     const float inv = 1.0f / DGS_CELL;
@@ -391,8 +439,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     if (rc) return rc;
 
     DgsDevHeader h;
-    DGS_CUDA(cudaMemcpyAsync(&h, hdr, sizeof(h), cudaMemcpyDeviceToHost, st));
-    DGS_CUDA(cudaStreamSynchronize(st));
+    rc = read_header(hdr, &h, st);
+    if (rc) return rc;
     DGS_REQUIRE(!(h.flags & DGS_HDR_OUTSIDE), DGS_ERR_SAMPLE_OUTSIDE_BOUNDS, "a sample lies outside the given bounds (or is NaN)");
     plan->num_rendered = h.num_rendered;
     plan->n_l1 = (uint64_t)(uint32_t)h.n_l1;
@@ -458,8 +506,10 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
                                  gb + plan->g_l1_mask_off, st);
         if (rc) return rc;
     }
-    DGS_CUDA(cudaMemcpyAsync(gb + plan->g_plan_off, plan, sizeof(*plan), cudaMemcpyHostToDevice, st));
-    DGS_CUDA(cudaMemcpyAsync(sb + plan->s_plan_off, plan, sizeof(*plan), cudaMemcpyHostToDevice, st));
+    static_assert(sizeof(dgs_plan_t) % 4 == 0 && sizeof(dgs_plan_t) <= 2048, "plan travels as a kernel argument");
+    dgs_store_plan_kernel<<<1, 64, 0, st>>>((uint32_t*)(gb + plan->g_plan_off), (uint32_t*)(sb + plan->s_plan_off), *plan);
+    DGS_NOTE_LAUNCHES(1);
+    DGS_LAUNCH_CHECK();
     return 0;
 }
 

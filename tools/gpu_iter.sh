@@ -13,7 +13,7 @@ echo "== bench ours"; timeout 900 python bench.py --steps 5 --warmup 3 > $O/benc
 fi
 if [ "${WITH_NCU:-0}" = "1" ]; then
 echo "== ncu"
-CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-per-function"
 timeout 600 $CMD > $O/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1
 echo "rc=$?"
