@@ -33,7 +33,9 @@
 #endif
 #define FWD_WARPS 4
 #define FWD_THREADS (FWD_WARPS * 32)
-#define FWD_CAPF 64   // staged fast records per warp (flushed when more than CAPF-32 are waiting)
+#ifndef FWD_CAPF
+#define FWD_CAPF 64   // staged fast records per warp (flushed when more than CAPF-32 are waiting); 96 and 128 measured no better
+#endif
 #define FWD_CAPG 32   // staged general records per warp
 #define FWD_QRAW 96   // queued survivor ids per warp (< 32 left over + 64 new)
 
