@@ -128,26 +128,46 @@ __device__ __forceinline__ void bwd_phi_grads(const float* a, const float* con, 
     }
 }
 
-// Single-channel form of the same VJP with the per-Gaussian factors pulled out of the pair loop (the way fn 0 keeps raw
+// The same VJP with the per-Gaussian factors pulled out of the pair loop (the way fn 0 keeps raw
 // moments).  With Phi = sum_u dO_u H_u(a, C), a = C X:
 //   dL/dv   =     sum_s G Phi
 //   dL/dmu  = v C sum_s G (dPhi/da - Phi X)                                      -> A1, C and v applied once per batch
 //   dL/dC_mn= v   sum_s [ B_m X_n (+ B_n X_m) + G dPhi/dC_mn|explicit ],  B = G (dPhi/da - Phi X / 2)
 // which saves the D x D product with C and about half of the conic arithmetic per pair.
-template <int D, int FN>
-__device__ __forceinline__ void bwd_pair_moments(const float* X, const float* a, float G, const float* con, const float* dOs,
-                                                 float& dV, float* A1, float* dC) {
+template <int D, int FN, int CB>
+__device__ __forceinline__ void bwd_pair_moments(const float* X, const float* a, float G, const float* con, const float* val,
+                                                 const float* dOs, float* dV, float* A1, float* dC) {
     constexpr int T = D * (D + 1) / 2;
     constexpr int U = dgs_nuniq(D, FN);
     float H[U];
     dgs_hermite<D, FN>(a, con, H);
-    float Phi = 0.f;
+    float Phi = 0.f, dPda[D], dPdC[T];
+    if (CB == 1) {
+        // one channel: v is applied once per batch, the weights are dO itself
 #pragma unroll
-    for (int u = 0; u < U; u++) Phi = fmaf(H[u], dOs[u], Phi);
-    float dPda[D], dPdC[T];
-    bwd_phi_grads<D, FN>(a, con, dOs, dPda, dPdC);
+        for (int u = 0; u < U; u++) Phi = fmaf(H[u], dOs[u], Phi);
+        dV[0] = fmaf(G, Phi, dV[0]);
+        bwd_phi_grads<D, FN>(a, con, dOs, dPda, dPdC);
+    } else {
+        // several channels: W_u = sum_c v_c dO_uc carries the values; dL/dv_c needs the per-channel sums
+        float Wu[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) Wu[u] = 0.f;
+#pragma unroll
+        for (int c = 0; c < CB; c++) {
+            float hd = 0.f;
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const float d_ = dOs[u * CB + c];
+                hd = fmaf(H[u], d_, hd);
+                Wu[u] = fmaf(val[c], d_, Wu[u]);
+            }
+            dV[c] = fmaf(G, hd, dV[c]);
+            Phi = fmaf(val[c], hd, Phi);
+        }
+        bwd_phi_grads<D, FN>(a, con, Wu, dPda, dPdC);
+    }
     const float GP = G * Phi, hGP = 0.5f * GP;
-    dV += GP;
     float B[D];
 #pragma unroll
     for (int m = 0; m < D; m++) {
@@ -229,9 +249,9 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
     using K = BwdCfg<D, FN, CB>;
     constexpr int T = K::T, U = K::U, SW = K::SW, SW0 = K::SW0;
     constexpr int PW = DGS_PREC_W(D);
-    // single channel, derivative orders: per-Gaussian factors are applied after the loop (bwd_pair_moments); D == 1 `third`
-    // keeps the literal reference expression of bwd_pair
-    constexpr bool MOMENTS = BWD_MOMENTS && FN > 0 && CB == 1 && !(D == 1 && FN == 3);
+    // derivative orders: per-Gaussian factors are applied after the loop (bwd_pair_moments); D == 1 `third` keeps the
+    // literal reference expression of bwd_pair
+    constexpr bool MOMENTS = BWD_MOMENTS && FN > 0 && !(D == 1 && FN == 3);
     uint32_t id[NG];
     bool valid[NG], exact[NG];
     float mu[NG][D], geo[NG][T], con[NG][T], val[NG][CB];
@@ -365,7 +385,7 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
 #pragma unroll
                     for (int j = i; j < D; j++) dC[g][dgs_tri(D, i, j)] = fmaf(wX[i], X[j], dC[g][dgs_tri(D, i, j)]);
             } else if constexpr (MOMENTS) {
-                bwd_pair_moments<D, FN>(X, a, Gv, con[g], sr + D, dV[g][0], dM[g], dC[g]);
+                bwd_pair_moments<D, FN, CB>(X, a, Gv, con[g], val[g], sr + D, dV[g], dM[g], dC[g]);
             } else {
                 bwd_pair<D, FN, CB>(X, a, Gv, con[g], val[g], sr + D, dV[g], dM[g], dC[g]);
             }
@@ -377,10 +397,11 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
         for (int g = 0; g < NG; g++) {
             float t[D];
             dgs_conic_times<D>(con[g], dM[g], t);
+            const float vs = CB == 1 ? val[g][0] : 1.0f;   // several channels: the values are inside the weights already
 #pragma unroll
-            for (int d = 0; d < D; d++) dM[g][d] = val[g][0] * t[d];
+            for (int d = 0; d < D; d++) dM[g][d] = vs * t[d];
 #pragma unroll
-            for (int k = 0; k < T; k++) dC[g][k] *= val[g][0];
+            for (int k = 0; k < T; k++) dC[g][k] *= vs;
         }
     }
 #pragma unroll
