@@ -610,6 +610,7 @@ static void bwd_launch_fn(BwdArgs a, int n_coarse, cudaStream_t st) {
         a.ch0 = ch;
         DGS_NOTE_LAUNCHES(1);
         if (left >= 4) { dgs_backward_kernel<D, FN, 4, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 4; }
+        else if (left == 3) { dgs_backward_kernel<D, FN, 3, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 3; }
         else if (left >= 2) { dgs_backward_kernel<D, FN, 2, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 2; }
         else if (FN == 0 && a.C == 1) { dgs_backward_kernel<D, FN, 1, FN == 0><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 1; }
         else { dgs_backward_kernel<D, FN, 1, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 1; }

@@ -381,6 +381,7 @@ static void fwd_launch_fn(FwdArgs a, int n_coarse, cudaStream_t st) {
         a.ch0 = ch;
         DGS_NOTE_LAUNCHES(1);
         if (left >= 4) { dgs_forward_kernel<D, FN, 4, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 4; }
+        else if (left == 3) { dgs_forward_kernel<D, FN, 3, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 3; }
         else if (left >= 2) { dgs_forward_kernel<D, FN, 2, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 2; }
         else { dgs_forward_kernel<D, FN, 1, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 1; }
     }
