@@ -120,3 +120,25 @@ def test_reuse_of_sample_binning_matches_fresh_preprocess():
     assert parity.norm_err(out.detach().cpu().numpy(), fresh["out_gaussian"].astype(np.float64)) <= 1e-6
     for k, tt in (("dmeans_", m2), ("dvalues_", v2), ("dconics_", cn2)):
         assert parity.bwd_err(tt.grad.cpu().numpy(), fresh[k + "gaussian"].astype(np.float64)) <= 1e-5
+
+
+@pytest.mark.parametrize("D,C", [(2, 5), (2, 6), (2, 7), (3, 7), (1, 9)])
+def test_many_channels_vs_cpu_oracle(D, C):
+    """C > 4 runs ceil(C / 4) traversals over channel blocks of 4, 3, 2 or 1 (csrc/dgs_forward.cu, fwd_launch_fn):
+    every block size and every offset `ch0` against the oracle, all four functions forward and backward."""
+    rng = np.random.default_rng(100 * D + C)
+    P = 300
+    m, v, cov, con = cases.make_gaussians(rng, P, D, C, {1: 0.02, 2: 0.06, 3: 0.15}[D], lo=-1.04, hi=1.04)
+    s = rng.uniform(-1, 1, (640, D)).astype(np.float32)
+    s[0, :], s[1, :] = -1.0, 1.0
+    c = dict(means=m, values=v, covariances=cov, conics=con, samples=np.ascontiguousarray(s))
+    name = f"many_channels_d{D}_c{C}"
+    got = parity.run_product(c, name=name)
+    orc = parity.oracle_all(c, name=name)
+    parity.assert_binning_equal(got, orc["pre"], name)
+    for f in parity.FN:
+        e = parity.fwd_err(got["out_" + f], orc["out_" + f], orc["abs_" + f])
+        assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
+        for k in ("dmeans_", "dvalues_", "dconics_"):
+            e = parity.bwd_err(got[k + f], orc[k + f])
+            assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
