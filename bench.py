@@ -39,7 +39,9 @@ WORKLOADS = {
     "cfg1": (2, 10_000, 256, 1),
     "cfg2": (2, 1_000_000, 4096, 1),
     "cfg3": (3, 1_000_000, 256, 1),
+    "cfg5": (3, 8_000_000, 512, 1),     # BASELINE.json configs[4]: the 512^3 grid is FIXED and split over the ranks
 }
+STRONG = {"cfg5"}                        # workloads whose global grid does not grow with the rank count
 METRIC = "fwd+bwd query points/sec at 1M Gaussians x 16.7M pts"
 UNIT = "points/s"
 
@@ -67,7 +69,11 @@ def make_inputs(workload, rank, world):
     rng = np.random.default_rng(0)
     m, v, cov, con = cases.make_gaussians(rng, P, D, C, cases.sigma_for(P, D))
     # weak scaling: the global grid has world*n points along axis 0; rank r owns rows [r*n, (r+1)*n)
-    ax0 = np.linspace(-1.0, 1.0, n * world, dtype=np.float64)[rank * n:(rank + 1) * n]
+    if workload in STRONG:
+        rows = n // world
+        ax0 = np.linspace(-1.0, 1.0, n, dtype=np.float64)[rank * rows:(rank + 1) * rows]
+    else:
+        ax0 = np.linspace(-1.0, 1.0, n * world, dtype=np.float64)[rank * n:(rank + 1) * n]
     ax = np.linspace(-1.0, 1.0, n, dtype=np.float64)
     mesh = np.meshgrid(ax0, *([ax] * (D - 1)), indexing="ij")
     s = np.stack([g.reshape(-1) for g in mesh], -1).astype(np.float32)
@@ -471,8 +477,8 @@ def main():
         pre_bytes = P * (4 * (D + T) + 8) + 12 * L + 24 * L + N * (4 * D + 12) + 24 * N
         line = {
             "metric": METRIC, "value": N * world * K / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-            "warmup": max(3, args.warmup), "ms_per_step": tot_ms / K, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "warmup": max(3, args.warmup), "ms_per_step": tot_ms / K, "higher_is_better": True,
+            "scaling": "strong" if args.workload in STRONG else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {D}D, P={P} Gaussians x {N} query points per GPU "
                                    f"({'x'.join([str(WORKLOADS[args.workload][2])] * D)} grid slab), C={C}, "
                                    f"fn={['gaussian', 'derivative', 'laplacian', 'third'][fn]}, "
