@@ -502,7 +502,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     rc = dgs_launch_l1_start(keys_s, (int64_t)plan->n_l1, plan->n_coarse, l1_start, st);
     if (rc) return rc;
     if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1_masks(plan, keys_s, l1_ids, crec, (const float*)(sb + plan->s_fine_aabb_off),
+        rc = dgs_launch_l1_masks(plan, l1_start, l1_ids, crec, (const float*)(sb + plan->s_fine_aabb_off),
                                  gb + plan->g_l1_mask_off, st);
         if (rc) return rc;
     }

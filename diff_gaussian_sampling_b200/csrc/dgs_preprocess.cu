@@ -687,17 +687,37 @@ int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uin
 // somewhere in the box of the samples of fine tile ft of that coarse tile.  Built once per
 // preprocess; the accumulation kernels only test a bit.  masks: [4][n] of u32 / u64.
 // ------------------------------------------------------------------------------------
+// One CTA per coarse tile: the boxes of its fine tiles (centre, half width) are set up once in shared memory, the
+// threads stride over the tile's list entries.  Level thresholds that do not depend on the fine tile are formed once per
+// entry (same products as DgsCullGeom::decide, so the masks are bit-identical to testing every level from scratch).
+#define DGS_MASK_THREADS 128
 template <int D, typename M>
-__global__ void __launch_bounds__(DGS_THREADS) dgs_l1_mask_kernel(const uint32_t* __restrict__ keys_sorted,
-                                                                  const uint32_t* __restrict__ l1_ids, int64_t n,
-                                                                  const float4* __restrict__ crec,
-                                                                  const float* __restrict__ fine_aabb, int fpcD, float tau,
-                                                                  float tau_max, M* __restrict__ masks) {
-    const int64_t e = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
-    if (e >= n) return;
-    const int64_t tile = keys_sorted[e];
-    const DgsCullRecView rec = dgs_crec_load<D>(crec, l1_ids[e]);
-    float sh[4], sh2[4], tt[4], st[4];
+__global__ void __launch_bounds__(DGS_MASK_THREADS) dgs_l1_mask_kernel(const uint32_t* __restrict__ l1_start,
+                                                                       const uint32_t* __restrict__ l1_ids, int64_t n,
+                                                                       const float4* __restrict__ crec,
+                                                                       const float* __restrict__ fine_aabb, int fpcD, float tau,
+                                                                       float tau_max, M* __restrict__ masks) {
+    __shared__ float s_ctr[64][3], s_half[64][3];
+    __shared__ unsigned long long s_valid;
+    const int64_t tile = blockIdx.x;
+    const uint32_t e0 = l1_start[tile], e1 = l1_start[tile + 1];
+    if (e0 == e1) return;
+    if (threadIdx.x == 0) s_valid = 0ull;
+    __syncthreads();
+    if ((int)threadIdx.x < fpcD) {
+        const int ft = threadIdx.x;
+        const float4 a = __ldg((const float4*)(fine_aabb + (tile * fpcD + ft) * 8));
+        const float4 b = __ldg((const float4*)(fine_aabb + (tile * fpcD + ft) * 8) + 1);
+        const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
+        DgsTileBox box;
+        box.set(lo, hi);
+#pragma unroll
+        for (int d = 0; d < 3; d++) { s_ctr[ft][d] = box.ctr[d]; s_half[ft][d] = box.half[d]; }
+        if (lo[0] <= hi[0]) atomicOr(&s_valid, 1ull << ft);   // has samples
+    }
+    __syncthreads();
+    const unsigned long long valid = s_valid;
+    float sh[4], sh2[4], tt[4], k2[4];
 #pragma unroll
     for (int l = 0; l < 4; l++) {
         const float tl = tau + DGS_TAU_STEP * (float)l;
@@ -705,44 +725,60 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_mask_kernel(const uint32_t
         sh2[l] = ratio < 1.f ? ratio * 1.00002f : 1.f;
         sh[l] = ratio < 1.f ? sqrtf(ratio) * 1.00001f : 1.f;
         tt[l] = 2.0f * tl;
-        st[l] = sqrtf(tt[l]);
+        k2[l] = 2.0f * sqrtf(tt[l]);
     }
-    const bool always = rec.rs2 < 0.f;
-    M m[4] = {0, 0, 0, 0};
-    for (int ft = 0; ft < fpcD; ft++) {
-        const float4 a = __ldg((const float4*)(fine_aabb + (tile * fpcD + ft) * 8));
-        const float4 b = __ldg((const float4*)(fine_aabb + (tile * fpcD + ft) * 8) + 1);
-        const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
-        if (!(lo[0] <= hi[0])) continue;   // no samples in this fine tile
-        if (always) {
+    for (uint32_t e = e0 + threadIdx.x; e < e1; e += DGS_MASK_THREADS) {
+        const DgsCullRecView rec = dgs_crec_load<D>(crec, l1_ids[e]);
+        M m[4] = {0, 0, 0, 0};
+        if (rec.rs2 < 0.f) {                    // never culled
 #pragma unroll
-            for (int l = 0; l < 4; l++) m[l] |= (M)1 << ft;
-            continue;
+            for (int l = 0; l < 4; l++) m[l] = (M)valid;
+        } else {
+            float rs2l[4], Rl[4][D < 3 ? D : 1];
+#pragma unroll
+            for (int l = 0; l < 4; l++) {
+                rs2l[l] = rec.rs2 * sh2[l];
+                if (D < 3) {
+#pragma unroll
+                    for (int d = 0; d < D; d++) Rl[l][d] = rec.R[d] * sh[l];
+                }
+            }
+            for (int ft = 0; ft < fpcD; ft++) {
+                if (!((valid >> ft) & 1ull)) continue;     // uniform over the CTA
+                DgsTileBox box;
+#pragma unroll
+                for (int d = 0; d < 3; d++) { box.ctr[d] = s_ctr[ft][d]; box.half[d] = s_half[ft][d]; }
+                DgsCullGeom<D> g;
+                g.measure(rec, box);
+                const float base = g.h2;
+#pragma unroll
+                for (int l = 3; l >= 0; l--) {
+                    bool ok = g.d2 <= rs2l[l];
+                    if (D < 3) {
+#pragma unroll
+                        for (int d = 0; d < D; d++) ok = ok && (g.dist[d] <= Rl[l][d]);
+                    }
+                    const float rhs = tt[l] + base + k2[l] * g.sq;
+                    ok = ok && (g.q <= fmaf(rhs, 1.001f, 1e-5f));
+                    m[l] |= (M)(ok ? 1 : 0) << ft;
+                }
+            }
         }
-        DgsTileBox box;
-        box.set(lo, hi);
-        DgsCullGeom<D> g;
-        g.measure(rec, box);
-        if (!g.decide(rec, sh[3], sh2[3], tt[3], st[3])) continue;   // levels are nested: 3 is the widest
-        m[3] |= (M)1 << ft;
 #pragma unroll
-        for (int l = 0; l < 3; l++)
-            if (g.decide(rec, sh[l], sh2[l], tt[l], st[l])) m[l] |= (M)1 << ft;
+        for (int l = 0; l < 4; l++) masks[(int64_t)l * n + e] = m[l];
     }
-#pragma unroll
-    for (int l = 0; l < 4; l++) masks[(int64_t)l * n + e] = m[l];
 }
 
-int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* keys_sorted, const uint32_t* l1_ids, const float4* crec,
+int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,
                         const float* fine_aabb, void* masks, cudaStream_t st) {
     const int64_t n = (int64_t)plan->n_l1;
     if (n <= 0) return 0;
-    const int nb = dgs_cdiv(n, DGS_THREADS);
+    const int nb = plan->n_coarse;
     const float tau = plan->tau, tau_max = plan->tau + DGS_TAU_MAX_EXTRA;
     const int f = plan->fine_per_coarse;
 #define MASK_LAUNCH(DD)                                                                                                   \
-    if (plan->mask_bytes == 8) dgs_l1_mask_kernel<DD, unsigned long long><<<nb, DGS_THREADS, 0, st>>>(keys_sorted, l1_ids, n, crec, fine_aabb, f, tau, tau_max, (unsigned long long*)masks); \
-    else dgs_l1_mask_kernel<DD, uint32_t><<<nb, DGS_THREADS, 0, st>>>(keys_sorted, l1_ids, n, crec, fine_aabb, f, tau, tau_max, (uint32_t*)masks);
+    if (plan->mask_bytes == 8) dgs_l1_mask_kernel<DD, unsigned long long><<<nb, DGS_MASK_THREADS, 0, st>>>(l1_start, l1_ids, n, crec, fine_aabb, f, tau, tau_max, (unsigned long long*)masks); \
+    else dgs_l1_mask_kernel<DD, uint32_t><<<nb, DGS_MASK_THREADS, 0, st>>>(l1_start, l1_ids, n, crec, fine_aabb, f, tau, tau_max, (uint32_t*)masks);
     if (plan->D == 1) { MASK_LAUNCH(1) } else if (plan->D == 2) { MASK_LAUNCH(2) } else { MASK_LAUNCH(3) }
 #undef MASK_LAUNCH
     DGS_NOTE_LAUNCHES(1);

@@ -22,5 +22,5 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const float
                   const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* n1, unsigned long long* n1bits, const uint32_t* n1_off,
                   uint32_t* keys, uint32_t* vals, cudaStream_t st);
 int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uint32_t* start, cudaStream_t st);
-int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* keys_sorted, const uint32_t* l1_ids, const float4* crec,
+int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,
                         const float* fine_aabb, void* masks, cudaStream_t st);
