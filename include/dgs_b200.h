@@ -9,7 +9,9 @@
  * Conventions
  *   - every pointer named *_dev is DEVICE memory owned by the caller; the library never
  *     allocates or frees memory the caller sees (reference: torch-owned tensors,
- *     sample_points.cu:54-63);
+ *     sample_points.cu:54-63).  Its only own allocation is one 96-byte pinned, mapped host
+ *     slot per calling host thread, through which the two synchronising calls read their
+ *     header back without touching a copy engine the caller may be keeping busy;
  *   - all floats are fp32, row-major, contiguous (reference: .contiguous().data<float>(),
  *     sample_points.cu:84-93);
  *   - `stream` is a cudaStream_t passed as void*; everything is enqueued on it.  Only
