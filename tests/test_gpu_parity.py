@@ -142,3 +142,26 @@ def test_many_channels_vs_cpu_oracle(D, C):
         for k in ("dmeans_", "dvalues_", "dconics_"):
             e = parity.bwd_err(got[k + f], orc[k + f])
             assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
+
+
+@pytest.mark.parametrize("D", [2, 3])
+def test_clustered_gaussians_vs_cpu_oracle(D):
+    """All Gaussians in one small cluster: a few coarse tiles carry lists of thousands of entries while most are empty
+    (long survivor queues, many flushes per fine tile, heavily unbalanced CTAs; the lists are thousands of entries long); plus points far from any Gaussian."""
+    rng = np.random.default_rng(500 + D)
+    P = 2000 if D == 2 else 1000
+    sig = 0.02 if D == 2 else 0.05
+    m, v, cov, con = cases.make_gaussians(rng, P, D, 2, sig)
+    m[:] = (0.31 + 0.75 * sig * rng.normal(size=(P, D))).astype(np.float32)
+    s = cases.grid_samples(40 if D == 2 else 14, D)
+    c = dict(means=m, values=v, covariances=cov, conics=con, samples=np.ascontiguousarray(s))
+    name = f"clustered_d{D}"
+    got = parity.run_product(c, fns=(0, 1, 2), name=name)
+    orc = parity.oracle_all(c, fns=(0, 1, 2), name=name)
+    parity.assert_binning_equal(got, orc["pre"], name)
+    for f in parity.FN[:3]:
+        e = parity.fwd_err(got["out_" + f], orc["out_" + f], orc["abs_" + f])
+        assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
+        for k in ("dmeans_", "dvalues_", "dconics_"):
+            e = parity.bwd_err(got[k + f], orc[k + f])
+            assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
