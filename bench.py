@@ -518,7 +518,7 @@ def main():
                                       "pipeline fill included"}
         if not args.no_cpu_baseline and world == 1:   # reported at N=1 only
             try:
-                line["cpu_baseline"] = cpu_port_baseline(args.workload, 16 if P >= 1_000_000 else 32)
+                line["cpu_baseline"] = cpu_port_baseline(args.workload, ({1: 1024, 2: 32, 3: 10}[D] if P >= 1_000_000 else min(WORKLOADS[args.workload][2], 256)))   # ~1e9 pairs: 10-30 s of CPU work
             except Exception as ex:  # noqa: BLE001
                 line["cpu_baseline"] = {"error": repr(ex)[:200]}
         print(json.dumps(line), flush=True)
