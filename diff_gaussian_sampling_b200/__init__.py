@@ -27,6 +27,7 @@ __all__ = [
     "GaussianSampler", "preprocess_gaussians", "preprocess_aggregate", "sample_gaussians",
     "sample_gaussians_derivative", "sample_gaussians_laplacian", "sample_gaussians_third_derivative",
     "aggregate_neighbors", "plan_of", "count_pairs", "covariances_from_scales_rotations", "sample_gaussians_jet",
+    "set_tuning",
 ]
 
 # ---------------------------------------------------------------------------------------
@@ -636,6 +637,11 @@ class _CovarianceFromScalesRotations(torch.autograd.Function):
 
 def covariances_from_scales_rotations(scales, rotations=None):
     return _CovarianceFromScalesRotations.apply(scales, rotations)
+
+
+def set_tuning(tile_target=0, fpc=0, T1=0):
+    """Overrides of the internal tile hierarchy (0 = automatic); see dgs_set_tuning in include/dgs_b200.h."""
+    _lib.load().dgs_set_tuning(int(tile_target), int(fpc), int(T1))
 
 
 def count_pairs(binning_buffer, sample_binning_buffer, num_rendered, fn=0) -> int:

@@ -49,6 +49,7 @@ EXPORTS = {
     "dgs_plan_sizeof": (c_sz, []),
     "dgs_last_error": (ctypes.c_char_p, []),
     "dgs_launch_count": (ctypes.c_ulonglong, []),
+    "dgs_set_tuning": (None, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
     "dgs_geom_bytes": (c_sz, [c_i64, c_i64, ctypes.c_int]),
     "dgs_public_bytes": (c_sz, [c_u64]),
     "dgs_plan_begin": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_i64, ctypes.c_int, c_vp, c_f32, c_vp, c_sz,

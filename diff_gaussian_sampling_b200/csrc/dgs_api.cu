@@ -3,6 +3,7 @@
 // (sample_points.cu:37-372) and sampler runtime (cuda_sampler/sampler_impl.cu:191-405).
 // Nothing here allocates device memory or touches torch.
 #include <math.h>
+#include <atomic>
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
@@ -10,7 +11,26 @@
 #include "dgs_preprocess.cuh"
 
 static thread_local char g_err[512] = "";
-unsigned long long g_dgs_launches = 0;
+std::atomic<unsigned long long> g_dgs_launches{0};
+
+// Tile-hierarchy overrides (0 = automatic).  Read ONCE from the environment when the library is loaded
+// (DGS_TILE_TARGET, DGS_FPC, DGS_T1: tuning sweeps) and settable through dgs_set_tuning (tests force the
+// multi-level hierarchy and the 64-bit mask path on small cases); choose_tiles only reads the atomics.
+static std::atomic<int> g_tune_target{0}, g_tune_fpc{0}, g_tune_t1{0};
+namespace {
+struct TuneInit {
+    TuneInit() {
+        if (const char* ev = getenv("DGS_TILE_TARGET")) { const int v = atoi(ev); if (v >= 8) g_tune_target = v; }
+        if (const char* ev = getenv("DGS_FPC")) { const int v = atoi(ev); if (v >= 1) g_tune_fpc = v; }
+        if (const char* ev = getenv("DGS_T1")) { const int v = atoi(ev); if (v >= 1) g_tune_t1 = v; }
+    }
+} g_tune_init;
+}
+extern "C" __attribute__((visibility("default"))) void dgs_set_tuning(int tile_target, int fpc, int T1) {
+    g_tune_target = tile_target >= 8 ? tile_target : 0;
+    g_tune_fpc = fpc >= 1 ? fpc : 0;
+    g_tune_t1 = T1 >= 1 ? T1 : 0;
+}
 void dgs_set_error(const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -210,18 +230,13 @@ static int choose_tiles(dgs_plan_t* pl) {
     if (cells_eff < 1.0) cells_eff = 1.0;
     const double per_cell = (double)pl->N / cells_eff;
     double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 110.0);
-    if (const char* ev = getenv("DGS_TILE_TARGET")) {          // tuning knob (samples per fine tile)
-        const double v = atof(ev);
-        if (v >= 8.0) target = v;
-    }
+    const int tune_target = g_tune_target.load(), tune_fpc = g_tune_fpc.load(), tune_t1 = g_tune_t1.load();
+    if (tune_target >= 8) target = (double)tune_target;   // samples per fine tile
     double f = pow(per_cell / target, 1.0 / D);
     int F = (int)floor(f);
     if (F < 1) F = 1;
     int fpc_default = D == 1 ? 8 : (D == 2 ? 4 : 3);
-    if (const char* ev = getenv("DGS_FPC")) {
-        const int v = atoi(ev);
-        if (v >= 1) fpc_default = v;
-    }
+    if (tune_fpc >= 1) fpc_default = tune_fpc;
     int T1 = (F + fpc_default - 1) / fpc_default;
     // keep a Gaussian's tau-box from covering too many coarse tiles (list entries ~ P * prod(2R/w + 1))
     if (pl->mean_extent > 0.f) {
@@ -230,10 +245,7 @@ static int choose_tiles(dgs_plan_t* pl) {
         if (cap < 1) cap = 1;
         if (T1 > cap) T1 = cap;
     }
-    if (const char* ev = getenv("DGS_T1")) {
-        const int v = atoi(ev);
-        if (v >= 1) T1 = v;
-    }
+    if (tune_t1 >= 1) T1 = tune_t1;
     if (T1 < 1) T1 = 1;
     // small problems: one CTA works on one coarse tile, so trade fine tiles per coarse tile for more coarse tiles
     // until the grid can fill the 148 SMs (cfg1: 21 -> 189 CTAs)
@@ -245,9 +257,10 @@ static int choose_tiles(dgs_plan_t* pl) {
             const int cap = (int)floor(k / (double)pl->mean_extent);
             t1_cap = cap < 1 ? 1 : (cap < F ? cap : F);
         }
-        while (T1 < t1_cap && (int64_t)pl->blocks * ipow_(T1, D) < 2 * 148 && !getenv("DGS_T1")) T1++;
+        while (T1 < t1_cap && (int64_t)pl->blocks * ipow_(T1, D) < 2 * 148 && tune_t1 < 1) T1++;
     }
     int fpc = (F + T1 - 1) / T1;
+    if (tune_fpc >= 1 && tune_t1 >= 1) fpc = tune_fpc;     // both forced: take the hierarchy literally
     const int fpc_max = D == 1 ? 64 : (D == 2 ? 8 : 4);
     if (fpc > fpc_max) fpc = fpc_max;
     // bound the number of tiles
@@ -591,4 +604,4 @@ extern "C" __attribute__((visibility("default"))) int dgs_count_pairs(const dgs_
 
 extern "C" __attribute__((visibility("default"))) size_t dgs_plan_sizeof(void) { return sizeof(dgs_plan_t); }
 
-extern "C" __attribute__((visibility("default"))) unsigned long long dgs_launch_count(void) { return g_dgs_launches; }
+extern "C" __attribute__((visibility("default"))) unsigned long long dgs_launch_count(void) { return g_dgs_launches.load(); }

@@ -503,7 +503,6 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                 while (nq >= 32 || (end && nq > 0)) {
                     const int cnt = nq < 32 ? nq : 32;
                     const bool pass = lane < cnt;
-                    const bool last = end && nq <= 32;
                     bool fast = false, exact = false;
                     uint32_t id = 0;
                     if (pass) {
@@ -548,15 +547,9 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         nf = rem;
                         __syncwarp();
                     }
-                    if (last && nf > 0) {
-                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane);
-                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane);
-                        nf = 0;
-                    }
-                    while (ng >= 32 || (last && ng > 0)) {
-                        const int c2 = ng < 32 ? ng : 32;
-                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, c2, lane);
-                        const int rem = ng - c2;          // < 32
+                    if (ng >= 32) {
+                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, 32, lane);
+                        const int rem = ng - 32;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qG[32 + lane];
                         __syncwarp();
@@ -566,7 +559,16 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     }
                     __syncwarp();
                 }
-                if (end) break;
+                if (end) {
+                    // leftovers (nf < 32 * NG, ng < 32) are processed here unconditionally: ids queued by an earlier
+                    // drain must not depend on a later chunk of the list having a survivor for this tile
+                    if (nf > 0) {
+                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane);
+                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane);
+                    }
+                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, ng, lane);
+                    break;
+                }
             }
         }
     }

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <atomic>
 #include "../../include/dgs_b200.h"
 
 #define DGS_CELL 0.51f           // config.h:18
@@ -15,8 +16,8 @@
 #define DGS_TAU_MAX_EXTRA 6.0f   // tile lists are built for tau + 3*step
 
 // --- launch accounting (bench.py reports gpu_launches) -------------------------------
-extern unsigned long long g_dgs_launches;
-#define DGS_NOTE_LAUNCHES(n) (g_dgs_launches += (unsigned long long)(n))
+extern std::atomic<unsigned long long> g_dgs_launches;
+#define DGS_NOTE_LAUNCHES(n) (g_dgs_launches.fetch_add((unsigned long long)(n), std::memory_order_relaxed))
 
 // --- error plumbing ------------------------------------------------------------------
 void dgs_set_error(const char* fmt, ...);

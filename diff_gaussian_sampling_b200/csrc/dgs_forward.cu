@@ -186,6 +186,24 @@ __device__ __forceinline__ void fwd_eval_general(const float* __restrict__ sG, i
     }
 }
 
+// dispatch on the number of samples per lane of this pass (compile-time S keeps x/acc in registers)
+template <int D, int FN, int CB>
+__device__ __forceinline__ void fwd_flush_fast(int s_eff, const float* __restrict__ sF, int nf,
+                                               const float (&x)[FwdCfg<D, FN, CB>::SMAX][D],
+                                               float (&acc)[FwdCfg<D, FN, CB>::SMAX][FwdCfg<D, FN, CB>::U][CB]) {
+    constexpr int SMAX = FwdCfg<D, FN, CB>::SMAX;
+    switch (s_eff) {
+        case 1: fwd_eval_fast<D, FN, CB, 1>(sF, nf, x, acc); break;
+        case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1>(sF, nf, x, acc); break;
+        case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1>(sF, nf, x, acc); break;
+        case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1>(sF, nf, x, acc); break;
+        case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1>(sF, nf, x, acc); break;
+        case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1>(sF, nf, x, acc); break;
+        case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1>(sF, nf, x, acc); break;
+        default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1>(sF, nf, x, acc); break;
+    }
+}
+
 template <int D, int FN, int CB, bool COUNT_ONLY>
 __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? FWD_TUNED : FWD_TUNED_3D) : FWD_MINB) dgs_forward_kernel(const FwdArgs A) {
     using K = FwdCfg<D, FN, CB>;
@@ -262,7 +280,6 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                 while (nq >= 32 || (end && nq > 0)) {
                     const int cnt = nq < 32 ? nq : 32;
                     const bool pass = lane < cnt;
-                    const bool last = end && nq <= 32;
                     bool fast = false, exact = false;
                     uint32_t id = 0;
                     float pr[PW];
@@ -321,26 +338,23 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     if (lane + 32 < rem) qR[32 + lane] = keep2;
                     nq = rem;
                     __syncwarp();
-                    if (nf > FWD_CAPF - 32 || (last && nf > 0)) {
-                        switch (s_eff) {
-                            case 1: fwd_eval_fast<D, FN, CB, 1>(sF, nf, x, acc); break;
-                            case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1>(sF, nf, x, acc); break;
-                            case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1>(sF, nf, x, acc); break;
-                            case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1>(sF, nf, x, acc); break;
-                            case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1>(sF, nf, x, acc); break;
-                            case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1>(sF, nf, x, acc); break;
-                            case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1>(sF, nf, x, acc); break;
-                            default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1>(sF, nf, x, acc); break;
-                        }
+                    if (nf > FWD_CAPF - 32) {
+                        fwd_flush_fast<D, FN, CB>(s_eff, sF, nf, x, acc);
                         nf = 0;
                     }
-                    if (ng > FWD_CAPG - 32 || (last && ng > 0)) {
+                    if (ng > FWD_CAPG - 32) {
                         fwd_eval_general<D, FN, CB>(sG, ng, s_eff, x, acc);
                         ng = 0;
                     }
                     __syncwarp();
                 }
-                if (end) break;
+                if (end) {
+                    // whatever is still staged is evaluated here, whether or not the last chunks of the list had a
+                    // survivor for this tile (records staged by an earlier drain must not depend on a later one)
+                    if (nf > 0) fwd_flush_fast<D, FN, CB>(s_eff, sF, nf, x, acc);
+                    if (ng > 0) fwd_eval_general<D, FN, CB>(sG, ng, s_eff, x, acc);
+                    break;
+                }
             }
             if (!COUNT_ONLY) {
 #pragma unroll

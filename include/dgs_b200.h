@@ -105,6 +105,15 @@ const char* dgs_last_error(void);
 /* number of CUDA kernels this library has launched in this process so far */
 unsigned long long dgs_launch_count(void);
 
+/*
+ * Overrides of the internal tile hierarchy that dgs_plan_begin chooses (0 = automatic): samples per fine tile,
+ * fine tiles per coarse-tile axis, coarse tiles per cell axis.  Process-wide; meant for tests (force the multi-level
+ * hierarchy and the 64-bit survivor masks on small inputs) and tuning sweeps.  The environment variables
+ * DGS_TILE_TARGET / DGS_FPC / DGS_T1 set the same three values once, when the library is loaded.  Results do not
+ * depend on the hierarchy beyond the stated tolerance (public binning arrays not at all).
+ */
+void dgs_set_tuning(int tile_target, int fpc, int T1);
+
 /* Bytes of the preprocess scratch ("geometry buffer"; reference GeometryState,
  * sampler_impl.cu:191-198 — radii live outside it here, as a caller tensor). */
 size_t dgs_geom_bytes(int64_t P, int64_t N, int D);

@@ -82,13 +82,24 @@ def membership(point_list: np.ndarray, ranges: np.ndarray, sample_cells: np.ndar
     return per_cell[cells].T  # (P,N)
 
 
+_PT_CACHE = {"key": None, "val": None}
+
+
 def _pair_terms(means, conics, samples, D):
+    # evaluate_by_cells calls forward / abs / backward / ... on the same chunk one after the other
+    key = (id(means), id(conics), id(samples), means.shape, samples.shape)
+    if _PT_CACHE["key"] == key:
+        return _PT_CACHE["val"]
     X = displacement(means, samples)                       # (P,N,D)
     Cm = conic_matrix(conics, D)                           # (P,D,D)
-    a = np.einsum("pij,pnj->pni", Cm, X)                   # a = C X
-    power = -0.5 * np.einsum("pni,pni->pn", a, X)
+    a = np.zeros_like(X)                                   # a = C X
+    for i in range(D):
+        for j in range(D):
+            a[:, :, i] += Cm[:, i, j][:, None] * X[:, :, j]
+    power = -0.5 * (a * X).sum(axis=2)
     ok = ~(power > 0.0)                                    # forward.cu:171,178
     G = np.where(ok, np.exp(np.minimum(power, 0.0)), 0.0)
+    _PT_CACHE["key"], _PT_CACHE["val"] = key, (X, Cm, a, G)
     return X, Cm, a, G
 
 
@@ -142,7 +153,9 @@ def abs_forward(fn, means, values, conics, samples, mult):
 #   dC_mn    = sum G * ( -k X_m X_n S + dS/da_m X_n + [m!=n] dS/da_n X_m + dS/dC_mn )
 #   k = 1/2 (m==n) else 1.
 # ----------------------------------------------------------------------------
-def backward_analytic(fn, means, values, conics, samples, mult, dout):
+def backward_analytic(fn, means, values, conics, samples, mult, dout, absolute=False):
+    """absolute=True returns, per gradient element, sum over pairs of |that pair's contribution| — the
+    cancellation-aware error scale of the gradient, like abs_forward for the field."""
     D = means.shape[1]
     P, N, C = means.shape[0], samples.shape[0], values.shape[1]
     idx = packed_index(D)
@@ -154,7 +167,10 @@ def backward_analytic(fn, means, values, conics, samples, mult, dout):
     Hf = H.reshape(P, N, A)
     dO = dout.astype(np.float64).reshape(N, A, C)
     v = values.astype(np.float64)
-    dV = np.einsum("pn,pna,nac->pc", GM, Hf, dO)
+    if absolute:
+        dV = np.einsum("pn,pna,nac->pc", np.abs(GM), np.abs(Hf), np.abs(dO))
+    else:
+        dV = np.einsum("pn,pna,nac->pc", GM, Hf, dO)
     w = np.einsum("pc,nac->pna", v, dO).reshape((P, N) + (D,) * ORDER[fn])
     S = np.einsum("pna,pna->pn", Hf, w.reshape(P, N, A))
     dSda = np.zeros((P, N, D))
@@ -178,7 +194,7 @@ def backward_analytic(fn, means, values, conics, samples, mult, dout):
             for n in range(m, D):
                 dSdC[:, :, idx[(m, n)]] = wa[:, :, m, m] if m == n else wa[:, :, m, n] + wa[:, :, n, m]
     dX = GM[:, :, None] * (-a * S[:, :, None] + np.einsum("pni,pim->pnm", dSda, Cm))
-    dmeans = dX.sum(axis=1)
+    dmeans = np.abs(dX).sum(axis=1) if absolute else dX.sum(axis=1)
     dcon = np.zeros((P, T))
     for m in range(D):
         for n in range(m, D):
@@ -186,7 +202,7 @@ def backward_analytic(fn, means, values, conics, samples, mult, dout):
             t = -k * X[:, :, m] * X[:, :, n] * S + dSda[:, :, m] * X[:, :, n] + dSdC[:, :, idx[(m, n)]]
             if m != n:
                 t = t + dSda[:, :, n] * X[:, :, m]
-            dcon[:, idx[(m, n)]] = (GM * t).sum(axis=1)
+            dcon[:, idx[(m, n)]] = np.abs(GM * t).sum(axis=1) if absolute else (GM * t).sum(axis=1)
     return dmeans, dV, dcon
 
 
@@ -320,3 +336,71 @@ def backward(fn, means, values, conics, samples, mult, dout):
     if means.shape[1] <= 2:
         return backward_reference(fn, means, values, conics, samples, mult, dout)
     return backward_analytic(fn, means, values, conics, samples, mult, dout)
+
+
+def abs_backward(fn, means, values, conics, samples, mult, dout):
+    """sum over pairs of |per-pair gradient contribution| for (dmeans, dvalues, dconics)."""
+    return backward_analytic(fn, means, values, conics, samples, mult, dout, absolute=True)
+
+
+# ----------------------------------------------------------------------------
+# Cell-by-cell evaluation: the same dense formulas, but only over the pairs the
+# reference evaluates (Gaussians listed in the sample's cell, forward.cu:104-162),
+# chunked so that a mid-size case (tens of thousands of points) stays in memory.
+# A Gaussian listed k times in a cell is evaluated k times, like the reference.
+# ----------------------------------------------------------------------------
+def pair_power(means, conics, samples):
+    """power[g,s] of forward.cu:171-178 (fp64 from the fp32-rounded displacement)."""
+    X, _, a, _ = _pair_terms(means, conics, samples, means.shape[1])
+    return -0.5 * np.einsum("pni,pni->pn", a, X)
+
+
+def evaluate_by_cells(fn, means, values, conics, samples, pre, dout=None, chunk_pairs=1_500_000, tau=None):
+    """pre: oracle.binning.preprocess(...) dict.  Returns dict(out, abs, [dmeans, dvalues, dconics,
+    abs_dmeans, abs_dvalues, abs_dconics]).  With tau: additionally cull / cull_d*: the same absolute sums
+    restricted to the pairs with power < -tau — exactly the mass an implementation that skips such pairs
+    (tau = 16 + 2 per derivative order) may leave out."""
+    P, D = means.shape
+    N, C = samples.shape[0], values.shape[1]
+    T = D * (D + 1) // 2
+    shape = (N,) + (D,) * ORDER[fn] + (C,)
+    res = dict(out=np.zeros(shape), abs=np.zeros(shape))
+    if tau is not None:
+        res["cull"] = np.zeros(shape)
+    if dout is not None:
+        for k, w in (("dmeans", D), ("dvalues", C), ("dconics", T)):
+            res[k] = np.zeros((P, w)); res["abs_" + k] = np.zeros((P, w))
+            if tau is not None:
+                res["cull_" + k] = np.zeros((P, w))
+    cells = (pre["s_keys_unsorted"] >> np.uint64(32)).astype(np.int64)
+    ranges = pre["ranges"]
+    order = np.argsort(cells, kind="stable")
+    bounds = np.searchsorted(cells[order], np.arange(ranges.shape[0] + 1))
+    for c in range(ranges.shape[0]):
+        lo, hi = int(ranges[c, 0]), int(ranges[c, 1])
+        sidx = order[bounds[c]:bounds[c + 1]]
+        if hi <= lo or sidx.size == 0:
+            continue
+        ids = pre["g_point_list"][lo:hi].astype(np.int64)
+        m, v, cn = means[ids], values[ids], conics[ids]
+        step = max(1, chunk_pairs // len(ids))
+        for b in range(0, sidx.size, step):
+            sl = sidx[b:b + step]
+            ss = samples[sl]
+            ones = np.ones((len(ids), len(sl)))
+            res["out"][sl] = forward(fn, m, v, cn, ss, ones)
+            res["abs"][sl] = abs_forward(fn, m, v, cn, ss, ones)
+            low = None
+            if tau is not None:
+                low = (pair_power(m, cn, ss) < -float(tau)).astype(np.float64)
+                res["cull"][sl] = abs_forward(fn, m, v, cn, ss, low) if low.any() else 0.0
+            if dout is not None:
+                g = dout[sl]
+                todo = [(("dmeans", "dvalues", "dconics"), backward(fn, m, v, cn, ss, ones, g)),
+                        (("abs_dmeans", "abs_dvalues", "abs_dconics"), abs_backward(fn, m, v, cn, ss, ones, g))]
+                if low is not None and low.any():
+                    todo.append((("cull_dmeans", "cull_dvalues", "cull_dconics"), abs_backward(fn, m, v, cn, ss, low, g)))
+                for keys, vals in todo:
+                    for k, x in zip(keys, vals):
+                        np.add.at(res[k], ids, x)
+    return res

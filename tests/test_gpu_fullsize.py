@@ -6,7 +6,10 @@ size-independent properties — the oracle cannot run at these sizes:
     backward, 1e-4 relative);
   * linearity in values: out(a v1 + b v2) == a out(v1) + b out(v2);
   * forward determinism (bit-identical reruns) and sampled agreement with a dense fp64 evaluation of the formula on a
-    random subset of points (tolerance 1e-5 of the local scale, membership taken from the public lists).
+    random subset of points (tolerance 1e-5 of the local scale, membership taken from the public lists);
+  * backward: for 64 random Gaussians, dL/dmeans, dL/dvalues and dL/dconics evaluated densely in fp64 over EVERY sample of
+    every cell that lists the Gaussian (public lists), compared per element against |ref| + sum|term| at 1e-4 — the
+    moments-form backward (csrc/dgs_backward.cu) at the size where its cancellation would show.
 """
 import numpy as np
 import pytest
@@ -23,6 +26,57 @@ def _inputs(D, P, n):
     rng = np.random.default_rng(0)
     m, v, cov, con = cases.make_gaussians(rng, P, D, 1, cases.sigma_for(P, D))
     return m, v, cov, con, cases.grid_samples(n, D)
+
+
+def _check_backward_of_random_gaussians(D, P, tm, tv, tcon, ts, dout, dm, dv, dc, g, rg, sb, srg, N, dev, n_sel=64):
+    """dense fp64 gradients of n_sel Gaussians over all samples of the cells that list them"""
+    import torch
+    ranges = rg.cpu().numpy().view(np.uint32).reshape(-1, 2)
+    sranges = srg.cpu().numpy().view(np.uint32).reshape(-1, 2)
+    s_list = torch.from_numpy(parity.split_public(sb, N)["point_list"].astype(np.int64)).to(dev)
+    cells_of = (g["keys_unsorted"] >> np.uint64(32)).astype(np.int64)
+    ids_of = g["point_list_unsorted"].astype(np.int64)
+    rng = np.random.default_rng(21)
+    sel = rng.choice(P, n_sel, replace=False)
+    idx = {(i, j): k for k, (i, j) in enumerate(cases.packed_pairs(D))}
+    worst = 0.0
+    n_checked = 0
+    for gid in sel:
+        cells = cells_of[ids_of == gid]                      # one entry per listing (duplicateWithKeys)
+        cells = cells[cells < len(sranges)]
+        if cells.size == 0:
+            assert float(dm[gid].abs().sum()) == 0.0 and float(dv[gid].abs().sum()) == 0.0
+            continue
+        sid = torch.cat([s_list[int(sranges[c, 0]):int(sranges[c, 1])] for c in cells])
+        if sid.numel() == 0:
+            continue
+        X = (tm[gid][None, :] - ts[sid]).double()            # fp32 subtraction, like the device
+        X = torch.where(X.abs() > 1.0, torch.where(X >= 0, torch.fmod(X, 2.0) - 2.0, torch.fmod(X, 2.0) + 2.0), X).float().double()
+        con = tcon[gid].double()
+        a = torch.stack([sum(con[idx[(min(i, j), max(i, j))]] * X[:, j] for j in range(D)) for i in range(D)], -1)
+        power = -0.5 * (a * X).sum(-1)
+        G = torch.where(power > 0, torch.zeros_like(power), torch.exp(torch.clamp(power, max=0.0)))
+        w = G * dout[sid, 0].double()
+        v = float(tv[gid, 0])
+        low = power < -16.0
+        ref_v, t_v = w.sum(), w.abs()
+        terms = {"dv": (w, dv[gid, 0])}
+        for d in range(D):
+            terms[f"dm{d}"] = (-v * w * a[:, d], dm[gid, d])
+        for (i, j), k in idx.items():
+            if i <= j:
+                terms[f"dc{k}"] = ((-0.5 if i == j else -1.0) * v * w * X[:, i] * X[:, j], dc[gid, k])
+        for name, (t, got) in terms.items():
+            ref, sc, cull = float(t.sum()), float(t.abs().sum()), float(t.abs()[low].sum())
+            err = max(abs(float(got) - ref) - cull * (1 + 1e-6), 0.0)
+            if sc > 0:
+                worst = max(worst, err / (abs(ref) + sc))
+            else:
+                assert float(got) == 0.0
+        n_checked += 1
+    assert n_checked >= n_sel // 2
+    assert worst <= 1e-4, f"full-size backward, worst per-element error {worst:.2e}"
+    print(f"full-size backward check: {n_checked} Gaussians, worst per-element error {worst:.2e}")
 
 
 @pytest.mark.parametrize("cfg", ["cfg2", "cfg3"])
@@ -68,6 +122,7 @@ def test_full_size_properties(cfg):
     scale = float((out.double().abs() * dout.double().abs()).sum())
     assert abs(lhs - rhs) <= 1e-4 * scale, (lhs, rhs, scale)
     assert torch.isfinite(dm).all() and torch.isfinite(dc).all()
+    _check_backward_of_random_gaussians(D, P, tm, tv, tcon, ts, dout, dm, dv, dc, g, rg, sb, srg, N, dev)
     v2 = torch.randn(P, 1, device=dev, generator=gen)
     out2 = dgs._C.sample_gaussians(*args(v2))
     out12 = dgs._C.sample_gaussians(*args(0.5 * tv - 2.0 * v2))

@@ -11,6 +11,11 @@ import parity
 
 pytestmark = pytest.mark.gpu
 
+# Product (fp32) against the fp64 ORACLE, per element and un-floored: the reference itself sits up to 1.2e-5 from the
+# oracle on tail-only points (tests/test_cpu_oracle.py), so this comparison allows 2e-5; product against the
+# reference's own GOLDEN outputs is held to the north_star's 1e-5.
+ORACLE_FWD_RTOL = 2e-5
+
 
 @pytest.mark.parametrize("name", cases.REFERENCE_CASES)
 def test_binning_bit_exact_vs_reference_golden(name):
@@ -28,15 +33,9 @@ def test_fields_and_grads_vs_reference_golden(name):
     c = cases.case(name)
     douts = {f: g["dout_" + f] for f in parity.FN}
     got = parity.run_product(c, name=name, douts=douts)
-    orc = parity.oracle_all(c, name=name, douts=douts)      # supplies the cancellation scale
-    for f in parity.FN:
-        e = parity.fwd_err(got["out_" + f], g["out_" + f].astype(np.float64), orc["abs_" + f])
-        assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
-        e = parity.norm_err(got["out_" + f], g["out_" + f].astype(np.float64))
-        assert e <= parity.FWD_RTOL, f"{name} {f} forward normwise err {e:.2e}"
-        for k in ("dmeans_", "dvalues_", "dconics_"):
-            e = parity.bwd_err(got[k + f], g[k + f].astype(np.float64))
-            assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
+    orc = parity.oracle_all(c, name=name, douts=douts)      # supplies the per-element scales and the cullable mass
+    worst = parity.assert_fields_and_grads(got, g, orc, (0, 1, 2, 3), name)
+    print(name, "worst per-element / normwise:", {k: (f"{a:.1e}", f"{b:.1e}") for k, (a, b) in worst.items()})
 
 
 @pytest.mark.parametrize("name", cases.REFERENCE_CASES + cases.OWN_3D_CASES)
@@ -45,14 +44,7 @@ def test_everything_vs_cpu_oracle(name):
     got = parity.run_product(c, name=name)
     orc = parity.oracle_all(c, name=name)
     parity.assert_binning_equal(got, orc["pre"], name)
-    for f in parity.FN:
-        e = parity.fwd_err(got["out_" + f], orc["out_" + f], orc["abs_" + f])
-        assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
-        e = parity.norm_err(got["out_" + f], orc["out_" + f])
-        assert e <= parity.FWD_RTOL, f"{name} {f} forward normwise err {e:.2e}"
-        for k in ("dmeans_", "dvalues_", "dconics_"):
-            e = parity.bwd_err(got[k + f], orc[k + f])
-            assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
+    parity.assert_fields_and_grads(got, orc, orc, (0, 1, 2, 3), name, fwd_rtol=ORACLE_FWD_RTOL)
 
 
 def test_forward_is_deterministic():
@@ -136,12 +128,7 @@ def test_many_channels_vs_cpu_oracle(D, C):
     got = parity.run_product(c, name=name)
     orc = parity.oracle_all(c, name=name)
     parity.assert_binning_equal(got, orc["pre"], name)
-    for f in parity.FN:
-        e = parity.fwd_err(got["out_" + f], orc["out_" + f], orc["abs_" + f])
-        assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
-        for k in ("dmeans_", "dvalues_", "dconics_"):
-            e = parity.bwd_err(got[k + f], orc[k + f])
-            assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
+    parity.assert_fields_and_grads(got, orc, orc, (0, 1, 2, 3), name, fwd_rtol=ORACLE_FWD_RTOL)
 
 
 @pytest.mark.parametrize("D", [2, 3])
@@ -159,9 +146,4 @@ def test_clustered_gaussians_vs_cpu_oracle(D):
     got = parity.run_product(c, fns=(0, 1, 2), name=name)
     orc = parity.oracle_all(c, fns=(0, 1, 2), name=name)
     parity.assert_binning_equal(got, orc["pre"], name)
-    for f in parity.FN[:3]:
-        e = parity.fwd_err(got["out_" + f], orc["out_" + f], orc["abs_" + f])
-        assert e <= parity.FWD_RTOL, f"{name} {f} forward err {e:.2e}"
-        for k in ("dmeans_", "dvalues_", "dconics_"):
-            e = parity.bwd_err(got[k + f], orc[k + f])
-            assert e <= parity.BWD_RTOL, f"{name} {f} {k} err {e:.2e}"
+    parity.assert_fields_and_grads(got, orc, orc, (0, 1, 2), name, fwd_rtol=ORACLE_FWD_RTOL)
