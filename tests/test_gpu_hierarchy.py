@@ -137,7 +137,8 @@ def test_midsize_natural_hierarchy_vs_dense_fp64(D, P, n, C, fns):
     name = f"mid_d{D}_p{P}_n{n}_c{C}"
     got = parity.run_product(c, fns=fns, name=name)
     pl = got["plan"]
-    assert pl["T1"] * pl["fpc"] > 1, pl
+    if s.shape[0] >= 100_000:                      # the 4,096-point 3D cases have 64 points per cell: no hierarchy there
+        assert pl["T1"] * pl["fpc"] > 1, pl
     ref = parity.dense64_all(c, got, fns=fns, name=name)
     worst = parity.assert_fields_and_grads(got, ref, ref, fns, name, fwd_rtol=ORACLE_FWD_RTOL)
     print(name, "T1", pl["T1"], "fpc", pl["fpc"], {k: f"{a:.1e}" for k, (a, b) in worst.items()})
