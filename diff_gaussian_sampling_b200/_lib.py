@@ -33,6 +33,7 @@ class Plan(ctypes.Structure):
         ("s_plan_off", c_u64), ("s_fine_start_off", c_u64), ("s_fine_ids_off", c_u64), ("s_fine_xyz_off", c_u64),
         ("s_fine_aabb_off", c_u64), ("s_coarse_aabb_off", c_u64), ("s_tmp_off", c_u64),
         ("g_prec_off", c_u64), ("g_l1_mask_off", c_u64), ("mask_bytes", c_i32), ("samples_reused", c_i32), ("reserved", c_i32 * 2),
+        ("g_sched_off", c_u64), ("reserved2", c_u64 * 3),
     ]
 
     def as_dict(self):
@@ -50,6 +51,8 @@ EXPORTS = {
     "dgs_last_error": (ctypes.c_char_p, []),
     "dgs_launch_count": (ctypes.c_ulonglong, []),
     "dgs_set_tuning": (None, [ctypes.c_int, ctypes.c_int, ctypes.c_int]),
+    "dgs_profile_enable": (None, [ctypes.c_int]),
+    "dgs_profile_dump": (ctypes.c_int, [ctypes.c_char_p, c_sz]),
     "dgs_geom_bytes": (c_sz, [c_i64, c_i64, ctypes.c_int]),
     "dgs_public_bytes": (c_sz, [c_u64]),
     "dgs_plan_begin": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_i64, ctypes.c_int, c_vp, c_f32, c_vp, c_sz,

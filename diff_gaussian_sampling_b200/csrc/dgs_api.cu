@@ -37,6 +37,55 @@ void dgs_set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+// ---- optional per-kernel timing ----
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+bool g_dgs_prof_on = false;
+namespace {
+struct ProfRec { const char* name; cudaEvent_t e0, e1; };
+std::vector<ProfRec> g_prof_recs;
+std::mutex g_prof_mu;
+}
+DgsProfScope::DgsProfScope(const char* n, cudaStream_t s) : name(n), st(s), e0(nullptr) {
+    if (!g_dgs_prof_on) return;
+    cudaEventCreate(&e0);
+    cudaEventRecord(e0, st);
+}
+DgsProfScope::~DgsProfScope() {
+    if (!e0) return;
+    cudaEvent_t e1;
+    cudaEventCreate(&e1);
+    cudaEventRecord(e1, st);
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    g_prof_recs.push_back({name, e0, e1});
+}
+extern "C" __attribute__((visibility("default"))) void dgs_profile_enable(int on) { g_dgs_prof_on = on != 0; }
+// Writes "name total_ms count" lines into buf (NUL-terminated, truncated to cap) and clears the records.  Synchronises the device.
+extern "C" __attribute__((visibility("default"))) int dgs_profile_dump(char* buf, size_t cap) {
+    cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    std::map<std::string, std::pair<double, int>> agg;
+    std::vector<std::string> order;
+    for (auto& r : g_prof_recs) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.e0, r.e1);
+        cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+        if (!agg.count(r.name)) order.push_back(r.name);
+        agg[r.name].first += ms; agg[r.name].second++;
+    }
+    g_prof_recs.clear();
+    std::string out;
+    for (auto& n : order) {
+        char line[160];
+        snprintf(line, sizeof(line), "%s %.6f %d\n", n.c_str(), agg[n].first, agg[n].second);
+        out += line;
+    }
+    if (buf && cap) { snprintf(buf, cap, "%s", out.c_str()); }
+    return (int)order.size();
+}
+
 extern "C" __attribute__((visibility("default"))) const char* dgs_last_error(void) { return g_err; }
 extern "C" __attribute__((visibility("default"))) int dgs_abi_version(void) { return DGS_ABI_VERSION; }
 
@@ -66,7 +115,7 @@ static PublicArrays public_arrays(void* buf, uint64_t L) {
 }
 
 struct GeomLayout {
-    size_t hdr, crec, crecR, touched, offsets, n1, n1_off, n1bits, scan_tmp, total;
+    size_t hdr, crec, crecR, touched, offsets, n1bits, scan_tmp, total;
 };
 static GeomLayout geom_layout(int64_t P, int D = 3) {
     GeomLayout g;
@@ -78,8 +127,6 @@ static GeomLayout geom_layout(int64_t P, int D = 3) {
     g.crecR = o; o = dgs_a128(o + p * 12);
     g.touched = o; o = dgs_a128(o + p * 4);
     g.offsets = o; o = dgs_a128(o + p * 4);
-    g.n1 = o; o = dgs_a128(o + p * 4);
-    g.n1_off = o; o = dgs_a128(o + p * 4);
     g.n1bits = o; o = dgs_a128(o + p * 8);
     g.scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes(p));
     g.total = o;
@@ -101,7 +148,7 @@ static uint32_t higher_msb(uint32_t n) {
     return msb;
 }
 
-static int ceil_log2(uint64_t n) {
+[[maybe_unused]] static int ceil_log2(uint64_t n) {
     int b = 0;
     while (((uint64_t)1 << b) < n) b++;
     return b;
@@ -109,7 +156,7 @@ static int ceil_log2(uint64_t n) {
 
 // sample-side temporary region (inside the sample binning buffer, after the persistent arrays)
 struct SampleTmp {
-    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, total;
+    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, l1_cnt, l1_start, l1_scan_tmp, total;
 };
 static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
     SampleTmp t;
@@ -121,6 +168,11 @@ static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
     t.scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes((int64_t)pl->n_fine + 1));
     t.alt_keys = o; if (pl->sort_bits > 8) o = dgs_a128(o + n * 8);
     t.alt_vals = o; if (pl->sort_bits > 8) o = dgs_a128(o + n * 4);
+    // Gaussian-side counters that must exist before the binning buffer does (its size depends on them): entries per
+    // coarse tile (later the emit cursors) and their exclusive scan
+    t.l1_cnt = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
+    t.l1_start = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
+    t.l1_scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes((int64_t)pl->n_coarse + 1));
     t.total = o;
     return t;
 }
@@ -140,20 +192,14 @@ static void sample_layout(dgs_plan_t* pl) {
 
 // Gaussian-side temporary region (inside the binning buffer)
 struct GaussTmp {
-    size_t l1_keys_u, l1_vals_u, l1_keys_s, l1_alt_k, l1_alt_v, l1_sort_tmp, pub_sort_tmp, pub_alt_k, pub_alt_v, total;
+    size_t l1_alt, pub_sort_tmp, pub_alt_k, pub_alt_v, total;
 };
 static GaussTmp gauss_tmp_layout(const dgs_plan_t* pl) {
     GaussTmp t;
     const size_t e = (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1);
     const size_t L = (size_t)(pl->num_rendered > 0 ? pl->num_rendered : 1);
-    const bool l1_multi = ceil_log2((uint64_t)pl->n_coarse) > 8;
     size_t o = 0;
-    t.l1_keys_u = o; o = dgs_a128(o + e * 4);
-    t.l1_vals_u = o; o = dgs_a128(o + e * 4);
-    t.l1_keys_s = o; o = dgs_a128(o + e * 4);
-    t.l1_alt_k = o; if (l1_multi) o = dgs_a128(o + e * 4);
-    t.l1_alt_v = o; if (l1_multi) o = dgs_a128(o + e * 4);
-    t.l1_sort_tmp = o; o = dgs_a128(o + dgs_sort_tmp_bytes(e));
+    t.l1_alt = o; o = dgs_a128(o + e * 4);              // ping-pong buffer of the per-tile id sort
     t.pub_sort_tmp = o; o = dgs_a128(o + dgs_sort_tmp_bytes(L));
     t.pub_alt_k = o; if (pl->sort_bits > 8) o = dgs_a128(o + L * 8);
     t.pub_alt_v = o; if (pl->sort_bits > 8) o = dgs_a128(o + L * 4);
@@ -165,6 +211,7 @@ static void gauss_layout(dgs_plan_t* pl) {
     const size_t p = (size_t)(pl->P > 0 ? pl->P : 1);
     size_t o = dgs_public_bytes((uint64_t)pl->num_rendered);
     pl->g_plan_off = o; o = dgs_a128(o + sizeof(dgs_plan_t));
+    pl->g_sched_off = o; o = dgs_a128(o + 128);
     pl->g_crec_off = o; o = dgs_a128(o + p * dgs_crec_bytes(pl->D));
     pl->g_l1_start_off = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     pl->g_l1_ids_off = o; o = dgs_a128(o + (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * 4);
@@ -400,8 +447,6 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     DgsDevHeader* hdr = (DgsDevHeader*)(g + gl.hdr);
     uint32_t* touched = (uint32_t*)(g + gl.touched);
     uint32_t* offsets = (uint32_t*)(g + gl.offsets);
-    uint32_t* n1 = (uint32_t*)(g + gl.n1);
-    uint32_t* n1_off = (uint32_t*)(g + gl.n1_off);
     void* gscan = g + gl.scan_tmp;
     const float4* crec = (const float4*)(g + gl.crec);
     const float* crecR = (const float*)(g + gl.crecR);
@@ -444,11 +489,14 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
 
     }
 
-    // --- size of the coarse-tile lists ---
-    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, n1,
-                       (unsigned long long*)(g + gl.n1bits), nullptr, nullptr, nullptr, st);
+    // --- size of the coarse-tile lists: entries per tile (atomic counters), scanned into the list starts ---
+    uint32_t* l1_cnt = (uint32_t*)(stmp + tl.l1_cnt);
+    uint32_t* l1_start_tmp = (uint32_t*)(stmp + tl.l1_start);
+    DGS_CUDA(cudaMemsetAsync(l1_cnt, 0, ((size_t)plan->n_coarse + 1) * 4, st));
+    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, l1_cnt,
+                       (unsigned long long*)(g + gl.n1bits), nullptr, st);
     if (rc) return rc;
-    rc = dgs_exclusive_scan_u32(n1, n1_off, P, gscan, (uint32_t*)&hdr->n_l1, st);
+    rc = dgs_exclusive_scan_u32(l1_cnt, l1_start_tmp, (int64_t)plan->n_coarse + 1, stmp + tl.l1_scan_tmp, (uint32_t*)&hdr->n_l1, st);
     if (rc) return rc;
 
     DgsDevHeader h;
@@ -485,7 +533,6 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     uint8_t* tmp = gb + plan->g_sort_tmp_off;
     PublicArrays pa = public_arrays(gb, L);
     const uint32_t* offsets = (const uint32_t*)(g + gl.offsets);
-    const uint32_t* n1_off = (const uint32_t*)(g + gl.n1_off);
 
     rc = dgs_launch_duplicate(means_dev, radii_dev, offsets, P, plan->D, plan, pa.keys_unsorted, pa.list_unsorted, st);
     if (rc) return rc;
@@ -500,22 +547,19 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     if (P > 0) DGS_CUDA(cudaMemcpyAsync(crec, g + gl.crec, (size_t)P * dgs_crec_bytes(plan->D), cudaMemcpyDeviceToDevice, st));
     uint32_t* l1_start = (uint32_t*)(gb + plan->g_l1_start_off);
     uint32_t* l1_ids = (uint32_t*)(gb + plan->g_l1_ids_off);
-    uint32_t* keys_u = (uint32_t*)(tmp + tl.l1_keys_u);
-    uint32_t* vals_u = (uint32_t*)(tmp + tl.l1_vals_u);
-    uint32_t* keys_s = (uint32_t*)(tmp + tl.l1_keys_s);
+    const SampleTmp stl = sample_tmp_layout(plan);
+    uint8_t* stmp = sb + plan->s_tmp_off;
+    uint32_t* cursor = (uint32_t*)(stmp + stl.l1_cnt);
     const float* coarse_aabb = (const float*)(sb + plan->s_coarse_aabb_off);
-    if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, nullptr,
-                           (unsigned long long*)(g + gl.n1bits), n1_off, keys_u, vals_u, st);
-        if (rc) return rc;
-        rc = dgs_sort_pairs_u32(keys_u, vals_u, keys_s, l1_ids, (uint32_t*)(tmp + tl.l1_alt_k), (uint32_t*)(tmp + tl.l1_alt_v),
-                                (int64_t)plan->n_l1, 0, ceil_log2((uint64_t)plan->n_coarse), tmp + tl.l1_sort_tmp, st);
-        if (rc) return rc;
-    }
-    rc = dgs_launch_l1_start(keys_s, (int64_t)plan->n_l1, plan->n_coarse, l1_start, st);
+    rc = dgs_launch_l1_cursor_init((const uint32_t*)(stmp + stl.l1_start), plan->n_coarse + 1, l1_start, cursor, st);
     if (rc) return rc;
     if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1_masks(plan, l1_start, l1_ids, crec, (const float*)(sb + plan->s_fine_aabb_off),
+        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, cursor,
+                           (unsigned long long*)(g + gl.n1bits), l1_ids, st);
+        if (rc) return rc;
+        rc = dgs_launch_l1_sort(plan, l1_start, l1_ids, (uint32_t*)(tmp + tl.l1_alt), st);
+        if (rc) return rc;
+        rc = dgs_launch_l1_masks(plan, l1_start, l1_ids, crec, (const float*)(sb + plan->s_fine_aabb_off), coarse_aabb,
                                  gb + plan->g_l1_mask_off, st);
         if (rc) return rc;
     }

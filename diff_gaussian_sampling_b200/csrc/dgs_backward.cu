@@ -47,6 +47,9 @@
 #endif
 #define BWD_WARPS 4
 #define BWD_THREADS (BWD_WARPS * 32)
+#ifndef BWD_GRAB
+#define BWD_GRAB 2    // fine tiles per grab of the work counter
+#endif
 #define BWD_QF 96    // fast-id queue slots per warp
 #define BWD_QG 64    // general-id queue slots per warp
 #define BWD_QRAW 96  // raw survivor-id queue slots per warp (< 32 left over + 64 new)
@@ -61,8 +64,10 @@ struct BwdArgs {
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
     const float* fine_aabb; const float* coarse_aabb;
     float* dmeans; float* dvalues; float* dconics;
+    uint32_t* sched;                              // work counter of this launch (zeroed by the launcher)
     int64_t N;
     int C, ch0, fpcD;
+    uint32_t n_tiles;                             // n_coarse * fpcD
 };
 
 template <int D, int FN, int CB>
@@ -70,9 +75,12 @@ struct BwdCfg {
     static constexpr int T = D * (D + 1) / 2;
     static constexpr int U = dgs_nuniq(D, FN);
     static constexpr int AFULL = dgs_nfull(D, FN);
-    static constexpr int SW0 = D + U * CB;                  // x | dOs[u][c]
+    // x | dOs[u][c] | fn 0 only: x'_i x'_j (i <= j), x' = x - centre of the tile's sample box (second moments are
+    // accumulated about that centre with ONE FFMA per component and pair, the operand coming straight from shared memory)
+    static constexpr int PO = D + U * CB;
+    static constexpr int SW0 = PO + (FN == 0 ? T : 0);
     static constexpr int SW = (SW0 + 3) / 4 * 4;
-    static constexpr int SAMP_FLOATS = 256 * SW < 2048 ? 256 * SW : 2048;
+    static constexpr int SAMP_FLOATS = 224 * SW < 2048 ? 224 * SW : 2048;
     static constexpr int SCAP = SAMP_FLOATS / SW;           // samples per pass
     static constexpr int G = FN == 0 ? 2 : (D <= 2 ? BWD_NG_HI : 1);   // Gaussians per lane on the fast path
     static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG + BWD_QRAW;
@@ -245,9 +253,9 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
 // staged samples.  FAST: whitened geometry without wrap; otherwise the literal reference pair.
 template <int D, int FN, int CB, int NG, bool FAST, bool VPOST>
 __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restrict__ sS, int np,
-                                          const uint32_t* __restrict__ queue, int count, int lane) {
+                                          const uint32_t* __restrict__ queue, int count, int lane, const float* ctr) {
     using K = BwdCfg<D, FN, CB>;
-    constexpr int T = K::T, U = K::U, SW = K::SW, SW0 = K::SW0;
+    constexpr int T = K::T, U = K::U, SW = K::SW, SW0 = K::SW0, PO = K::PO;
     constexpr int PW = DGS_PREC_W(D);
     // derivative orders: per-Gaussian factors are applied after the loop (bwd_pair_moments); D == 1 `third` keeps the
     // literal reference expression of bwd_pair
@@ -374,16 +382,25 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
                     }
                     w = Gv * S;
                 }
-                float wX[D];
+                if (FAST) {
+                    // first moment about the mean from the displacement at hand, second moment about the tile centre
+                    // from the sample's own products (converted after the loop): D + T FFMA per pair
 #pragma unroll
-                for (int d = 0; d < D; d++) {
-                    wX[d] = w * X[d];
-                    dM[g][d] += wX[d];
+                    for (int d = 0; d < D; d++) dM[g][d] = fmaf(w, X[d], dM[g][d]);
+#pragma unroll
+                    for (int k = 0; k < T; k++) dC[g][k] = fmaf(w, sr[PO + k], dC[g][k]);
+                } else {
+                    float wX[D];
+#pragma unroll
+                    for (int d = 0; d < D; d++) {
+                        wX[d] = w * X[d];
+                        dM[g][d] += wX[d];
+                    }
+#pragma unroll
+                    for (int i = 0; i < D; i++)
+#pragma unroll
+                        for (int j = i; j < D; j++) dC[g][dgs_tri(D, i, j)] = fmaf(wX[i], X[j], dC[g][dgs_tri(D, i, j)]);
                 }
-#pragma unroll
-                for (int i = 0; i < D; i++)
-#pragma unroll
-                    for (int j = i; j < D; j++) dC[g][dgs_tri(D, i, j)] = fmaf(wX[i], X[j], dC[g][dgs_tri(D, i, j)]);
             } else if constexpr (MOMENTS) {
                 bwd_pair_moments<D, FN, CB>(X, a, Gv, con[g], val[g], sr + D, dV[g], dM[g], dC[g]);
             } else {
@@ -392,6 +409,31 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
         }
     }
     }   // scalar path
+    if constexpr (FN == 0 && FAST && !(BWD_PACKED && VPOST && NG == 2 && CB == 1)) {
+        // sum w X X^T = S2' + mu' m1^T + m1 mu'^T - mu' mu'^T W,  S2' = sum w x' x'^T, mu' = mu - centre, m1 = sum w X, W = sum w
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            float W = 0.f;
+            if (VPOST) W = dV[g][0];
+            else {
+#pragma unroll
+                for (int c = 0; c < CB; c++) W = fmaf(val[g][c], dV[g][c], W);
+            }
+            float mp[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) mp[d] = mu[g][d] - ctr[d];
+#pragma unroll
+            for (int i = 0; i < D; i++)
+#pragma unroll
+                for (int j = i; j < D; j++) {
+                    float c2 = dC[g][dgs_tri(D, i, j)];
+                    c2 = fmaf(mp[i], dM[g][j], c2);
+                    c2 = fmaf(mp[j], dM[g][i], c2);
+                    c2 = fmaf(-(mp[i] * mp[j]), W, c2);
+                    dC[g][dgs_tri(D, i, j)] = c2;
+                }
+        }
+    }
     if constexpr (MOMENTS) {
 #pragma unroll
         for (int g = 0; g < NG; g++) {
@@ -430,21 +472,32 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     uint32_t* qF = (uint32_t*)(sS + K::SAMP_FLOATS);
     uint32_t* qG = qF + BWD_QF;
     uint32_t* qR = qG + BWD_QG;
-    const int64_t coarse = blockIdx.x;
-    if (__float_as_int(A.coarse_aabb[coarse * 8 + 6]) == 0) return;
-    const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
-    if (g0 == g1) return;
-
-    for (int ft = warp; ft < A.fpcD; ft += BWD_WARPS) {
-        const int64_t tile = coarse * A.fpcD + ft;
+    // persistent warps pulling fine tiles from a global counter (see dgs_forward.cu)
+    uint32_t nx = 0;
+    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)BWD_GRAB);
+    for (;;) {
+    const uint32_t grab = __shfl_sync(0xffffffffu, nx, 0);
+    if (grab >= A.n_tiles) break;
+    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)BWD_GRAB);
+    for (uint32_t gj = 0; gj < BWD_GRAB; gj++) {
+        const uint32_t tile32 = grab + gj;
+        if (tile32 >= A.n_tiles) break;
+        const int64_t tile = tile32;
+        const int64_t coarse = tile / A.fpcD;
+        const int ft = (int)(tile - coarse * A.fpcD);
         const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
         if (s0 == s1) continue;
+        const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
+        if (g0 == g1) continue;
         float lo[3], hi[3];
         {
             const float4 b0 = *(const float4*)(A.fine_aabb + tile * 8);
             const float4 b1 = *(const float4*)(A.fine_aabb + tile * 8 + 4);
             lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b0.w; hi[1] = b1.x; hi[2] = b1.y;
         }
+        float ctr[3];
+#pragma unroll
+        for (int d = 0; d < 3; d++) ctr[d] = 0.5f * (lo[d] + hi[d]);
 
         const uint32_t n = s1 - s0;
         const uint32_t n_pass = (n + SCAP - 1) / SCAP;
@@ -479,6 +532,15 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                 for (int u = 0; u < U; u++)
 #pragma unroll
                     for (int c = 0; c < CB; c++) r[D + u * CB + c] = ds[u][c];
+                if (FN == 0) {
+                    float xc[D];
+#pragma unroll
+                    for (int d = 0; d < D; d++) xc[d] = r[d] - ctr[d];
+#pragma unroll
+                    for (int i = 0; i < D; i++)
+#pragma unroll
+                        for (int j = i; j < D; j++) r[K::PO + dgs_tri(D, i, j)] = xc[i] * xc[j];
+                }
             }
             __syncwarp();
 
@@ -538,7 +600,7 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     nq = remq;
                     __syncwarp();
                     if (nf >= 32 * NG) {
-                        bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane);
+                        bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane, ctr);
                         const int rem = nf - 32 * NG;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qF[32 * NG + lane];
@@ -548,7 +610,7 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         __syncwarp();
                     }
                     if (ng >= 32) {
-                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, 32, lane);
+                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, 32, lane, ctr);
                         const int rem = ng - 32;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qG[32 + lane];
@@ -563,14 +625,15 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     // leftovers (nf < 32 * NG, ng < 32) are processed here unconditionally: ids queued by an earlier
                     // drain must not depend on a later chunk of the list having a survivor for this tile
                     if (nf > 0) {
-                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane);
-                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane);
+                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane, ctr);
+                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane, ctr);
                     }
-                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, ng, lane);
+                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, ng, lane, ctr);
                     break;
                 }
             }
         }
+    }
     }
 }
 
@@ -604,34 +667,58 @@ float dgs_tau_for(const dgs_plan_t* plan, int fn);
 int dgs_mask_level(int fn);
 int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st);
 
+template <typename KernelT>
+static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
+    static int cached[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = dev < 0 || dev >= 64 ? 0 : dev;
+    if (cached[dev] == 0) {
+        int sms = 148, occ = 1;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, BWD_THREADS, 0) != cudaSuccess || occ < 1) { occ = 1; (void)cudaGetLastError(); }
+        cached[dev] = sms * occ;
+    }
+    const int64_t need = ((int64_t)n_tiles + BWD_WARPS * BWD_GRAB - 1) / (BWD_WARPS * BWD_GRAB);
+    return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
+}
+
+template <int D, int FN, int CB, bool VPOST>
+static void bwd_launch_one(const BwdArgs& a, cudaStream_t st) {
+    auto kernel = dgs_backward_kernel<D, FN, CB, VPOST>;
+    DGS_PROF("backward_kernel", st);
+    cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
+    kernel<<<bwd_persistent_grid(kernel, a.n_tiles), BWD_THREADS, 0, st>>>(a);
+    DGS_NOTE_LAUNCHES(1);
+}
+
 template <int D, int FN>
-static void bwd_launch_fn(BwdArgs a, int n_coarse, cudaStream_t st) {
+static void bwd_launch_fn(BwdArgs a, cudaStream_t st) {
     int ch = 0;
     while (ch < a.C) {
         const int left = a.C - ch;
         a.ch0 = ch;
-        DGS_NOTE_LAUNCHES(1);
-        if (left >= 4) { dgs_backward_kernel<D, FN, 4, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 4; }
-        else if (left == 3) { dgs_backward_kernel<D, FN, 3, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 3; }
-        else if (left >= 2) { dgs_backward_kernel<D, FN, 2, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 2; }
-        else if (FN == 0 && a.C == 1) { dgs_backward_kernel<D, FN, 1, FN == 0><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 1; }
-        else { dgs_backward_kernel<D, FN, 1, false><<<n_coarse, BWD_THREADS, 0, st>>>(a); ch += 1; }
+        if (left >= 4) { bwd_launch_one<D, FN, 4, false>(a, st); ch += 4; }
+        else if (left == 3) { bwd_launch_one<D, FN, 3, false>(a, st); ch += 3; }
+        else if (left >= 2) { bwd_launch_one<D, FN, 2, false>(a, st); ch += 2; }
+        else if (FN == 0 && a.C == 1) { bwd_launch_one<D, FN, 1, FN == 0>(a, st); ch += 1; }
+        else { bwd_launch_one<D, FN, 1, false>(a, st); ch += 1; }
     }
 }
 
 template <int D>
-static void bwd_launch_d(const BwdArgs& a, int fn, int n_coarse, int64_t P, cudaStream_t st) {
+static void bwd_launch_d(const BwdArgs& a, int fn, int64_t P, cudaStream_t st) {
     switch (fn) {
         case 0:
-            bwd_launch_fn<D, 0>(a, n_coarse, st);
+            bwd_launch_fn<D, 0>(a, st);
             dgs_bwd_finalize_kernel<D><<<dgs_cdiv(P, DGS_THREADS), DGS_THREADS, 0, st>>>(a.conics, a.values, P, a.C == 1 ? 1 : 0,
                                                                                         a.dmeans, a.dconics);
             DGS_NOTE_LAUNCHES(1);
             break;
-        case 1: bwd_launch_fn<D, 1>(a, n_coarse, st); break;
-        case 2: bwd_launch_fn<D, 2>(a, n_coarse, st); break;
-        case 3: bwd_launch_fn<D, 3>(a, n_coarse, st); break;
-        default: bwd_launch_fn<D, DGS_FN_JET>(a, n_coarse, st); break;
+        case 1: bwd_launch_fn<D, 1>(a, st); break;
+        case 2: bwd_launch_fn<D, 2>(a, st); break;
+        case 3: bwd_launch_fn<D, 3>(a, st); break;
+        default: bwd_launch_fn<D, DGS_FN_JET>(a, st); break;
     }
 }
 
@@ -655,6 +742,8 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
     a.dmeans = dmeans; a.dvalues = dvalues; a.dconics = dconics;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
+    a.sched = (uint32_t*)(gbuf + plan->g_sched_off) + 1;     // the forward's counter is word 0
+    a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
     const int T = plan->D * (plan->D + 1) / 2;
     // the kernels accumulate: start from zero whatever the caller left in the buffers
     DGS_CUDA(cudaMemsetAsync(dmeans, 0, (size_t)plan->P * plan->D * 4, st));
@@ -662,9 +751,9 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     DGS_CUDA(cudaMemsetAsync(dconics, 0, (size_t)plan->P * T * 4, st));
     int rc = dgs_launch_pack(means, conics, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
     if (rc) return rc;
-    if (plan->D == 1) bwd_launch_d<1>(a, fn, plan->n_coarse, plan->P, st);
-    else if (plan->D == 2) bwd_launch_d<2>(a, fn, plan->n_coarse, plan->P, st);
-    else bwd_launch_d<3>(a, fn, plan->n_coarse, plan->P, st);
+    if (plan->D == 1) bwd_launch_d<1>(a, fn, plan->P, st);
+    else if (plan->D == 2) bwd_launch_d<2>(a, fn, plan->P, st);
+    else bwd_launch_d<3>(a, fn, plan->P, st);
     DGS_LAUNCH_CHECK();
     return 0;
 }

@@ -19,6 +19,17 @@
 extern std::atomic<unsigned long long> g_dgs_launches;
 #define DGS_NOTE_LAUNCHES(n) (g_dgs_launches.fetch_add((unsigned long long)(n), std::memory_order_relaxed))
 
+// --- optional per-kernel timing (dgs_profile_enable / dgs_profile_dump; off by default: one bool test per launch) ---
+// In-pipeline CUDA-event times per launcher, i.e. with the cache state of the real step (an ncu launch list flushes
+// the caches and serialises).  Events are recorded on the launch stream; nothing synchronises until the dump.
+extern bool g_dgs_prof_on;
+struct DgsProfScope {
+    const char* name; cudaStream_t st; cudaEvent_t e0;
+    DgsProfScope(const char* n, cudaStream_t s);
+    ~DgsProfScope();
+};
+#define DGS_PROF(name, st) DgsProfScope dgs_prof_scope_(name, st)
+
 // --- error plumbing ------------------------------------------------------------------
 void dgs_set_error(const char* fmt, ...);
 #define DGS_CUDA(call)                                                                   \

@@ -33,6 +33,9 @@
 #endif
 #define FWD_WARPS 4
 #define FWD_THREADS (FWD_WARPS * 32)
+#ifndef FWD_GRAB
+#define FWD_GRAB 2    // fine tiles per grab of the work counter
+#endif
 #ifndef FWD_CAPF
 #define FWD_CAPF 64   // staged fast records per warp (flushed when more than CAPF-32 are waiting); 96 and 128 measured no better
 #endif
@@ -49,8 +52,10 @@ struct FwdArgs {
     float* out;
     float* out1; float* out2;                     // jet: derivative (N, D, C) and Hessian (N, D, D, C); `out` is the value
     unsigned long long* pair_counter;
+    uint32_t* sched;                              // work counter of this launch (zeroed by the launcher)
     int64_t N;
     int C, ch0, fpcD;
+    uint32_t n_tiles;                             // n_coarse * fpcD
 };
 
 template <int D, int FN, int CB>
@@ -217,15 +222,27 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     float* sF = smem + (COUNT_ONLY ? 0 : warp * K::WARP_FLOATS);
     float* sG = sF + (COUNT_ONLY ? 0 : FWD_CAPF * FW);
     uint32_t* qR = s_qraw + (COUNT_ONLY ? 0 : warp * FWD_QRAW);
-    const int64_t coarse = blockIdx.x;
-    if (__float_as_int(A.coarse_aabb[coarse * 8 + 6]) == 0) return;   // no samples here
-    const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
     unsigned long long pairs = 0;
 
-    for (int ft = warp; ft < A.fpcD; ft += FWD_WARPS) {
-        const int64_t tile = coarse * A.fpcD + ft;
+    // Persistent warps: every warp pulls FWD_GRAB consecutive fine tiles at a time from a global counter (the next grab is
+    // issued before the current tiles are worked on, so its latency is hidden).  Tiles of one coarse tile are adjacent, so
+    // the warps of an SM mostly share coarse lists in L1/L2; no static assignment means no tail (round 1: one CTA per
+    // coarse tile, 12 % of the SM cycles idle at the end of the forward kernel).
+    uint32_t nx = 0;                                   // lane 0: the grab in flight
+    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)FWD_GRAB);
+    for (;;) {
+    const uint32_t grab = __shfl_sync(0xffffffffu, nx, 0);
+    if (grab >= A.n_tiles) break;
+    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)FWD_GRAB);
+    for (uint32_t gj = 0; gj < FWD_GRAB; gj++) {
+        const uint32_t tile32 = grab + gj;
+        if (tile32 >= A.n_tiles) break;
+        const int64_t tile = tile32;
+        const int64_t coarse = tile / A.fpcD;
+        const int ft = (int)(tile - coarse * A.fpcD);
         const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
         if (s0 == s1) continue;
+        const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
         float lo[3], hi[3];
         {
             const float4 b0 = *(const float4*)(A.fine_aabb + tile * 8);
@@ -377,6 +394,7 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
             }
         }
     }
+    }
     if (COUNT_ONLY) {
         // every lane carries the same per-warp count
         if (lane == 0 && pairs) atomicAdd(A.pair_counter, pairs);
@@ -387,28 +405,53 @@ float dgs_tau_for(const dgs_plan_t* plan, int fn) { return plan->tau + DGS_TAU_S
 // survivor-mask level of a function code: the jet uses the list of its highest order (levels are nested)
 int dgs_mask_level(int fn) { return fn == DGS_FN_JET ? 2 : (fn < 0 ? 0 : (fn > 3 ? 3 : fn)); }
 
+// grid of a persistent kernel: resident CTAs per SM x SMs, at most one warp per grab of work
+template <typename KernelT>
+static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
+    static int cached[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = dev < 0 || dev >= 64 ? 0 : dev;
+    if (cached[dev] == 0) {
+        int sms = 148, occ = 1;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, FWD_THREADS, 0) != cudaSuccess || occ < 1) { occ = 1; (void)cudaGetLastError(); }
+        cached[dev] = sms * occ;
+    }
+    const int64_t need = ((int64_t)n_tiles + FWD_WARPS * FWD_GRAB - 1) / (FWD_WARPS * FWD_GRAB);
+    return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
+}
+
+template <int D, int FN, int CB, bool COUNT_ONLY>
+static void fwd_launch_one(const FwdArgs& a, cudaStream_t st) {
+    auto kernel = dgs_forward_kernel<D, FN, CB, COUNT_ONLY>;
+    DGS_PROF(COUNT_ONLY ? "forward_count_only" : "forward_kernel", st);
+    cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
+    kernel<<<fwd_persistent_grid(kernel, a.n_tiles), FWD_THREADS, 0, st>>>(a);
+    DGS_NOTE_LAUNCHES(1);
+}
+
 template <int D, int FN>
-static void fwd_launch_fn(FwdArgs a, int n_coarse, cudaStream_t st) {
+static void fwd_launch_fn(FwdArgs a, cudaStream_t st) {
     int ch = 0;
     while (ch < a.C) {
         const int left = a.C - ch;
         a.ch0 = ch;
-        DGS_NOTE_LAUNCHES(1);
-        if (left >= 4) { dgs_forward_kernel<D, FN, 4, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 4; }
-        else if (left == 3) { dgs_forward_kernel<D, FN, 3, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 3; }
-        else if (left >= 2) { dgs_forward_kernel<D, FN, 2, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 2; }
-        else { dgs_forward_kernel<D, FN, 1, false><<<n_coarse, FWD_THREADS, 0, st>>>(a); ch += 1; }
+        if (left >= 4) { fwd_launch_one<D, FN, 4, false>(a, st); ch += 4; }
+        else if (left == 3) { fwd_launch_one<D, FN, 3, false>(a, st); ch += 3; }
+        else if (left >= 2) { fwd_launch_one<D, FN, 2, false>(a, st); ch += 2; }
+        else { fwd_launch_one<D, FN, 1, false>(a, st); ch += 1; }
     }
 }
 
 template <int D>
-static void fwd_launch_d(const FwdArgs& a, int fn, int n_coarse, cudaStream_t st) {
+static void fwd_launch_d(const FwdArgs& a, int fn, cudaStream_t st) {
     switch (fn) {
-        case 0: fwd_launch_fn<D, 0>(a, n_coarse, st); break;
-        case 1: fwd_launch_fn<D, 1>(a, n_coarse, st); break;
-        case 2: fwd_launch_fn<D, 2>(a, n_coarse, st); break;
-        case 3: fwd_launch_fn<D, 3>(a, n_coarse, st); break;
-        default: fwd_launch_fn<D, DGS_FN_JET>(a, n_coarse, st); break;
+        case 0: fwd_launch_fn<D, 0>(a, st); break;
+        case 1: fwd_launch_fn<D, 1>(a, st); break;
+        case 2: fwd_launch_fn<D, 2>(a, st); break;
+        case 3: fwd_launch_fn<D, 3>(a, st); break;
+        default: fwd_launch_fn<D, DGS_FN_JET>(a, st); break;
     }
 }
 
@@ -434,19 +477,20 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
     a.out = out; a.out1 = out_derivative; a.out2 = out_hessian; a.pair_counter = pair_counter;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
+    a.sched = (uint32_t*)(gbuf + plan->g_sched_off);
+    a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
     if (pair_counter) {
-        DGS_NOTE_LAUNCHES(1);
-        if (plan->D == 1) dgs_forward_kernel<1, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);
-        else if (plan->D == 2) dgs_forward_kernel<2, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);
-        else dgs_forward_kernel<3, 0, 1, true><<<plan->n_coarse, FWD_THREADS, 0, st>>>(a);
+        if (plan->D == 1) fwd_launch_one<1, 0, 1, true>(a, st);
+        else if (plan->D == 2) fwd_launch_one<2, 0, 1, true>(a, st);
+        else fwd_launch_one<3, 0, 1, true>(a, st);
         DGS_LAUNCH_CHECK();
         return 0;
     }
     int rc = dgs_launch_pack(means, conics, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
     if (rc) return rc;
-    if (plan->D == 1) fwd_launch_d<1>(a, fn, plan->n_coarse, st);
-    else if (plan->D == 2) fwd_launch_d<2>(a, fn, plan->n_coarse, st);
-    else fwd_launch_d<3>(a, fn, plan->n_coarse, st);
+    if (plan->D == 1) fwd_launch_d<1>(a, fn, st);
+    else if (plan->D == 2) fwd_launch_d<2>(a, fn, st);
+    else fwd_launch_d<3>(a, fn, st);
     DGS_LAUNCH_CHECK();
     return 0;
 }

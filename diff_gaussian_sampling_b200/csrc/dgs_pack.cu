@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_pack_kernel(const float* __re
 }
 
 int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st) {
+    DGS_PROF("pack", st);
     if (P <= 0) return 0;
     const int nb = dgs_cdiv(P, DGS_THREADS);
     if (D == 1) dgs_pack_kernel<1><<<nb, DGS_THREADS, 0, st>>>(means, conics, P, prec);

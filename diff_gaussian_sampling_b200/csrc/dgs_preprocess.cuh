@@ -19,8 +19,9 @@ int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const 
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
                          float* coarse_aabb, cudaStream_t st);
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
-                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* n1, unsigned long long* n1bits, const uint32_t* n1_off,
-                  uint32_t* keys, uint32_t* vals, cudaStream_t st);
-int dgs_launch_l1_start(const uint32_t* keys_sorted, int64_t n, int n_tiles, uint32_t* start, cudaStream_t st);
+                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* tile_cnt, unsigned long long* n1bits,
+                  uint32_t* ids, cudaStream_t st);
+int dgs_launch_l1_cursor_init(const uint32_t* start_tmp, int n, uint32_t* start_out, uint32_t* cursor, cudaStream_t st);
+int dgs_launch_l1_sort(const dgs_plan_t* plan, const uint32_t* l1_start, uint32_t* l1_ids, uint32_t* alt, cudaStream_t st);
 int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,
-                        const float* fine_aabb, void* masks, cudaStream_t st);
+                        const float* fine_aabb, const float* coarse_aabb, void* masks, cudaStream_t st);

@@ -111,6 +111,7 @@ size_t dgs_scan_tmp_bytes(int64_t n) { return dgs_a128((size_t)(dgs_cdiv(n > 0 ?
 
 template <bool INCLUSIVE>
 static int scan_impl(const uint32_t* in, uint32_t* out, int64_t n, void* tmp, uint32_t* total_out, cudaStream_t st) {
+    DGS_PROF("scan", st);
     if (n <= 0) {
         if (total_out) DGS_CUDA(cudaMemsetAsync(total_out, 0, 4, st));
         return 0;
@@ -240,6 +241,7 @@ size_t dgs_sort_tmp_bytes(int64_t n) {
 template <typename K>
 static int sort_impl(const K* keys_in, const uint32_t* vals_in, K* keys_out, uint32_t* vals_out, K* keys_alt,
                      uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit, void* tmp, cudaStream_t st) {
+    DGS_PROF(sizeof(K) == 8 ? "radix_sort_u64(incl. scan)" : "radix_sort_u32(incl. scan)", st);
     if (n <= 0) return 0;
     const int bits = end_bit - begin_bit;
     const int passes = bits <= 0 ? 0 : (bits + 7) / 8;

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DGS_ABI_VERSION 4
+#define DGS_ABI_VERSION 5
 #define DGS_ERR_BAD_ARG 10001
 #define DGS_ERR_UNSUPPORTED 10002
 #define DGS_ERR_BUFFER_TOO_SMALL 10003
@@ -97,6 +97,8 @@ typedef struct dgs_plan {
     int32_t  mask_bytes;           /* 4 (fine_per_coarse <= 32) or 8 bytes per mask                              */
     int32_t  samples_reused;       /* 1: the sample side of the buffers was carried over (dgs_plan_reuse_samples) */
     int32_t  reserved[2];
+    uint64_t g_sched_off;          /* two uint32 work counters of the persistent accumulation kernels (forward, backward) */
+    uint64_t reserved2[3];
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
@@ -113,6 +115,14 @@ unsigned long long dgs_launch_count(void);
  * depend on the hierarchy beyond the stated tolerance (public binning arrays not at all).
  */
 void dgs_set_tuning(int tile_target, int fpc, int T1);
+
+/*
+ * Optional per-kernel timing for tuning: after dgs_profile_enable(1) every kernel launcher brackets its launches with
+ * CUDA events on the launch stream (no synchronisation); dgs_profile_dump synchronises the device, writes one
+ * "name total_ms count" line per launcher into buf and clears the records.  Off by default.
+ */
+void dgs_profile_enable(int on);
+int  dgs_profile_dump(char* buf, size_t cap);
 
 /* Bytes of the preprocess scratch ("geometry buffer"; reference GeometryState,
  * sampler_impl.cu:191-198 — radii live outside it here, as a caller tensor). */

@@ -148,7 +148,7 @@ def _run_reference(c, fns, douts):
     """The unmodified reference extension on the same inputs -> dict shaped like parity.run_product's."""
     import torch
     ref = refload.load()
-    refload.raise_malloc_heap(4 << 30)
+    refload.raise_malloc_heap(8 << 30)
     dev = torch.device("cuda:0")
     t = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in c.items()}
     N = c["samples"].shape[0]
@@ -194,7 +194,7 @@ def test_product_vs_live_reference(P, n, fns):
     ref = _run_reference(c, fns, douts)
     parity.assert_binning_equal(got, ref, name)
     pl = got["plan"]
-    assert pl["T1"] > 1 and pl["fpc"] > 1, pl
+    assert pl["T1"] * pl["fpc"] > 1, pl
     scale = parity.dense64_all(c, got, fns=fns, name=name, douts=douts)
     worst = parity.assert_fields_and_grads(got, ref, scale, fns, name)
     print(name, "T1", pl["T1"], "fpc", pl["fpc"], {k: (f"{a:.1e}", f"{b:.1e}") for k, (a, b) in worst.items()})

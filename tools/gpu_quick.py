@@ -31,8 +31,12 @@ def main():
     N = s.shape[0]
     calls = [dgs.sample_gaussians, dgs.sample_gaussians_derivative, dgs.sample_gaussians_laplacian,
              dgs.sample_gaussians_third_derivative, dgs.sample_gaussians_jet]   # fn 4: value + derivative + Hessian fused
+    prof = os.environ.get("DGS_QUICK_PROFILE")
+    lib = dgs._lib.load()
     for rep in range(4):
         torch.cuda.synchronize()
+        if prof and rep == 3:
+            lib.dgs_profile_enable(1)
         e0 = ev()
         pre = dgs.preprocess_gaussians(tm, tv, tcov, tcon, ts, False)
         e1 = ev()
@@ -53,6 +57,12 @@ def main():
                    n_l1=plan.n_l1, mean_extent=plan.mean_extent, exact_wrap=plan.exact_wrap)
         rec["pts_per_s_fb"] = N / ((rec["t_fwd_ms"] + rec["t_bwd_ms"]) * 1e-3)
         rec["pts_per_s_all"] = N / ((rec["t_pre_ms"] + rec["t_fwd_ms"] + rec["t_bwd_ms"]) * 1e-3)
+    if prof:
+        import ctypes
+        buf = ctypes.create_string_buffer(1 << 16)
+        lib.dgs_profile_dump(buf, len(buf))
+        lib.dgs_profile_enable(0)
+        rec["kernel_ms"] = {ln.split()[0]: round(float(ln.split()[1]), 4) for ln in buf.value.decode().splitlines() if ln.strip()}
     rec["pairs"] = dgs.count_pairs(gb, sb, nr, fn)
     rec["pairs_per_pt"] = rec["pairs"] / N
     rec["fwd_pairs_per_s"] = rec["pairs"] / (rec["t_fwd_ms"] * 1e-3)
