@@ -665,7 +665,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_bwd_finalize_kernel(const flo
 
 float dgs_tau_for(const dgs_plan_t* plan, int fn);
 int dgs_mask_level(int fn);
-int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st);
+int dgs_launch_pack(const float* means, const float* conics, const float* values, int C, int64_t P, int D, float* prec, cudaStream_t st);
 
 template <typename KernelT>
 static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
@@ -749,7 +749,7 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     DGS_CUDA(cudaMemsetAsync(dmeans, 0, (size_t)plan->P * plan->D * 4, st));
     DGS_CUDA(cudaMemsetAsync(dvalues, 0, (size_t)plan->P * C * 4, st));
     DGS_CUDA(cudaMemsetAsync(dconics, 0, (size_t)plan->P * T * 4, st));
-    int rc = dgs_launch_pack(means, conics, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
+    int rc = dgs_launch_pack(means, conics, values, C, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
     if (rc) return rc;
     if (plan->D == 1) bwd_launch_d<1>(a, fn, plan->P, st);
     else if (plan->D == 2) bwd_launch_d<2>(a, fn, plan->P, st);

@@ -56,6 +56,7 @@ struct FwdArgs {
     int64_t N;
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
+    int prec_has_value;                           // C == 1: the packed records carry values[:, 0] (dgs_pack.cu)
 };
 
 template <int D, int FN, int CB>
@@ -69,10 +70,21 @@ struct FwdCfg {
     static constexpr int FW = (FW0 + 1) / 2 * 2;
     static constexpr int GW0 = D + T + CB + 1;                             // mu | conic | v | exact flag
     static constexpr int GW = (GW0 + 1) / 2 * 2;
-    static constexpr int WARP_FLOATS = FWD_CAPF * FW + FWD_CAPG * GW;
+    static constexpr int PW = DGS_PREC_W(D);
+    static constexpr bool PIPE = (FN == 0 && CB == 1);                      // cp.async gather straight from the packed records
+    static constexpr int FAST_FLOATS = (PIPE && 2 * 32 * PW > FWD_CAPF * FW) ? 2 * 32 * PW : FWD_CAPF * FW;
+    static constexpr int WARP_FLOATS = FAST_FLOATS + FWD_CAPG * GW;
 };
 
-template <int D, int FN, int CB, int S>
+__device__ __forceinline__ void dgs_cp_async16(void* smem_dst, const void* gsrc) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void dgs_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void dgs_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int D, int FN, int CB, int S, int STRIDE = FwdCfg<D, FN, CB>::FW>
 __device__ __forceinline__ void fwd_eval_fast(const float* __restrict__ sF, int nf,
                                               const float (&x)[FwdCfg<D, FN, CB>::SMAX][D],
                                               float (&acc)[FwdCfg<D, FN, CB>::SMAX][FwdCfg<D, FN, CB>::U][CB]) {
@@ -94,7 +106,7 @@ __device__ __forceinline__ void fwd_eval_fast(const float* __restrict__ sF, int 
             float r[FW];
 #pragma unroll
             for (int q = 0; q < FW / 2; q++) {
-                const float2 v = *(const float2*)(sF + k * FW + q * 2);
+                const float2 v = *(const float2*)(sF + k * STRIDE + q * 2);
                 r[q * 2] = v.x; r[q * 2 + 1] = v.y;
             }
             float2 U2[T];
@@ -192,20 +204,20 @@ __device__ __forceinline__ void fwd_eval_general(const float* __restrict__ sG, i
 }
 
 // dispatch on the number of samples per lane of this pass (compile-time S keeps x/acc in registers)
-template <int D, int FN, int CB>
+template <int D, int FN, int CB, int STRIDE = FwdCfg<D, FN, CB>::FW>
 __device__ __forceinline__ void fwd_flush_fast(int s_eff, const float* __restrict__ sF, int nf,
                                                const float (&x)[FwdCfg<D, FN, CB>::SMAX][D],
                                                float (&acc)[FwdCfg<D, FN, CB>::SMAX][FwdCfg<D, FN, CB>::U][CB]) {
     constexpr int SMAX = FwdCfg<D, FN, CB>::SMAX;
     switch (s_eff) {
-        case 1: fwd_eval_fast<D, FN, CB, 1>(sF, nf, x, acc); break;
-        case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1>(sF, nf, x, acc); break;
-        case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1>(sF, nf, x, acc); break;
-        case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1>(sF, nf, x, acc); break;
-        case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1>(sF, nf, x, acc); break;
-        case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1>(sF, nf, x, acc); break;
-        case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1>(sF, nf, x, acc); break;
-        default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1>(sF, nf, x, acc); break;
+        case 1: fwd_eval_fast<D, FN, CB, 1, STRIDE>(sF, nf, x, acc); break;
+        case 2: if (SMAX >= 2) fwd_eval_fast<D, FN, CB, SMAX >= 2 ? 2 : 1, STRIDE>(sF, nf, x, acc); break;
+        case 3: if (SMAX >= 3) fwd_eval_fast<D, FN, CB, SMAX >= 3 ? 3 : 1, STRIDE>(sF, nf, x, acc); break;
+        case 4: if (SMAX >= 4) fwd_eval_fast<D, FN, CB, SMAX >= 4 ? 4 : 1, STRIDE>(sF, nf, x, acc); break;
+        case 5: if (SMAX >= 5) fwd_eval_fast<D, FN, CB, SMAX >= 5 ? 5 : 1, STRIDE>(sF, nf, x, acc); break;
+        case 6: if (SMAX >= 6) fwd_eval_fast<D, FN, CB, SMAX >= 6 ? 6 : 1, STRIDE>(sF, nf, x, acc); break;
+        case 7: if (SMAX >= 7) fwd_eval_fast<D, FN, CB, SMAX >= 7 ? 7 : 1, STRIDE>(sF, nf, x, acc); break;
+        default: if (SMAX >= 8) fwd_eval_fast<D, FN, CB, SMAX >= 8 ? 8 : 1, STRIDE>(sF, nf, x, acc); break;
     }
 }
 
@@ -220,7 +232,7 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     float* sF = smem + (COUNT_ONLY ? 0 : warp * K::WARP_FLOATS);
-    float* sG = sF + (COUNT_ONLY ? 0 : FWD_CAPF * FW);
+    float* sG = sF + (COUNT_ONLY ? 0 : K::FAST_FLOATS);
     uint32_t* qR = s_qraw + (COUNT_ONLY ? 0 : warp * FWD_QRAW);
     unsigned long long pairs = 0;
 
@@ -271,6 +283,109 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     for (int c = 0; c < CB; c++) acc[i][u][c] = 0.f;
             }
 
+            if constexpr (K::PIPE && !COUNT_ONLY) {
+              if (A.prec_has_value) {
+                // ---- pipelined path (gaussian, one channel): the packed record [mu | U | v | id | flags] is the staged
+                // record.  A drain issues the cp.async gather of 32 records into one half of a double buffer and then
+                // evaluates the batch gathered by the PREVIOUS drain, so the L2 latency of a gather is covered by a whole
+                // batch of arithmetic; the (mask, id) words of the next 64 list entries are loaded one chunk ahead. ----
+                float* raw = sF;
+                int nq = 0, cnt_prev = 0, cur = 0;
+                auto process = [&](const float* buf, int cnt) {
+                    // wrap / far Gaussians (rare: tiles at the torus seam) go through the literal path; their value is
+                    // zeroed in the fast record, which is then evaluated harmlessly
+                    bool gen = false, exact = false;
+                    float* me = const_cast<float*>(buf) + lane * PW;
+                    if (lane < cnt) {
+                        bool fast = (__float_as_uint(me[PW - 1]) & DGS_PREC_FAST) != 0u;
+#pragma unroll
+                        for (int d = 0; d < D; d++) {
+                            const float xmin = me[d] - hi[d], xmax = me[d] - lo[d];
+                            if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;
+                            if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;
+                        }
+                        gen = !fast;
+                    }
+                    const uint32_t balG = __ballot_sync(0xffffffffu, gen);
+                    if (balG) {
+                        if (gen) {
+                            const uint32_t id = __float_as_uint(me[PW - 2]);
+                            float* r = sG + __popc(balG & lt) * GW;
+#pragma unroll
+                            for (int d = 0; d < D; d++) r[d] = me[d];
+#pragma unroll
+                            for (int k = 0; k < T; k++) r[D + k] = A.conics[(int64_t)id * T + k];
+                            r[D + T] = me[D + T];
+                            r[GW0 - 1] = exact ? 1.f : 0.f;
+#pragma unroll
+                            for (int k = 0; k <= D + T; k++) me[k] = 0.f;     // fast path then sees mu = 0, U = 0, v = 0: adds exactly 0
+                        }
+                        __syncwarp();
+                    }
+                    fwd_flush_fast<D, FN, CB, PW>(s_eff, buf, cnt, x, acc);
+                    if (balG) fwd_eval_general<D, FN, CB>(sG, __popc(balG), s_eff, x, acc);
+                    __syncwarp();
+                };
+                // chunk prefetch registers
+                uint32_t pid0 = 0, pid1 = 0;
+                bool pp0 = false, pp1 = false;
+                auto prefetch = [&](uint32_t base) {
+                    const uint32_t e0 = base + lane, e1 = e0 + 32;
+                    pp0 = pp1 = false; pid0 = pid1 = 0;
+                    if (e0 < g1) { pp0 = dgs_mask_bit(A.mask, A.mask64, e0, ft); pid0 = A.l1_ids[e0]; }
+                    if (e1 < g1) { pp1 = dgs_mask_bit(A.mask, A.mask64, e1, ft); pid1 = A.l1_ids[e1]; }
+                };
+                prefetch(g0);
+                for (uint32_t base = g0;; base += 64) {
+                    const bool p0 = pp0, p1 = pp1;
+                    const uint32_t id0 = pid0, id1 = pid1;
+                    const bool end = base + 64 >= g1;
+                    if (!end) prefetch(base + 64);
+                    const uint32_t b0 = __ballot_sync(0xffffffffu, p0), b1 = __ballot_sync(0xffffffffu, p1);
+                    if (p0) qR[nq + __popc(b0 & lt)] = id0;
+                    nq += __popc(b0);
+                    if (p1) qR[nq + __popc(b1 & lt)] = id1;
+                    nq += __popc(b1);
+                    __syncwarp();
+                    while (nq >= 32 || (end && nq > 0)) {
+                        const int cnt = nq < 32 ? nq : 32;
+                        if (lane < cnt) {
+                            const float* src = A.prec + (int64_t)qR[lane] * PW;
+                            float* dst = raw + (cur * 32 + lane) * PW;
+#pragma unroll
+                            for (int q = 0; q < PW / 4; q++) dgs_cp_async16(dst + 4 * q, src + 4 * q);
+                        }
+                        dgs_cp_async_commit();
+                        const int rem = nq - cnt;
+                        uint32_t keep = 0, keep2 = 0;
+                        if (lane < rem) keep = qR[32 + lane];
+                        if (lane + 32 < rem) keep2 = qR[64 + lane];
+                        __syncwarp();
+                        if (lane < rem) qR[lane] = keep;
+                        if (lane + 32 < rem) qR[32 + lane] = keep2;
+                        nq = rem;
+                        if (cnt_prev) {
+                            dgs_cp_async_wait<1>();
+                            __syncwarp();
+                            process(raw + (cur ^ 1) * 32 * PW, cnt_prev);
+                        }
+                        cnt_prev = cnt;
+                        cur ^= 1;
+                        __syncwarp();
+                    }
+                    if (end) {
+                        if (cnt_prev) {
+                            dgs_cp_async_wait<0>();
+                            __syncwarp();
+                            process(raw + (cur ^ 1) * 32 * PW, cnt_prev);
+                        }
+                        break;
+                    }
+                }
+                goto tile_pass_done;
+              }
+            }
+            {
             int nf = 0, ng = 0, nq = 0;
             for (uint32_t base = g0;; base += 64) {
                 // ---- survivors of this fine tile among the next 64 list entries -> raw id queue ----
@@ -373,6 +488,8 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     break;
                 }
             }
+            }
+        tile_pass_done:
             if (!COUNT_ONLY) {
 #pragma unroll
                 for (int i = 0; i < SMAX; i++) {
@@ -455,7 +572,7 @@ static void fwd_launch_d(const FwdArgs& a, int fn, cudaStream_t st) {
     }
 }
 
-int dgs_launch_pack(const float* means, const float* conics, int64_t P, int D, float* prec, cudaStream_t st);
+int dgs_launch_pack(const float* means, const float* conics, const float* values, int C, int64_t P, int D, float* prec, cudaStream_t st);
 
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                        const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
@@ -478,6 +595,7 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     a.out = out; a.out1 = out_derivative; a.out2 = out_hessian; a.pair_counter = pair_counter;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
     a.sched = (uint32_t*)(gbuf + plan->g_sched_off);
+    a.prec_has_value = 0;
     a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
     if (pair_counter) {
         if (plan->D == 1) fwd_launch_one<1, 0, 1, true>(a, st);
@@ -486,8 +604,9 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
         DGS_LAUNCH_CHECK();
         return 0;
     }
-    int rc = dgs_launch_pack(means, conics, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
+    int rc = dgs_launch_pack(means, conics, values, C, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
     if (rc) return rc;
+    a.prec_has_value = C == 1 ? 1 : 0;
     if (plan->D == 1) fwd_launch_d<1>(a, fn, st);
     else if (plan->D == 2) fwd_launch_d<2>(a, fn, st);
     else fwd_launch_d<3>(a, fn, st);

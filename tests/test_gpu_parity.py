@@ -34,7 +34,12 @@ def test_fields_and_grads_vs_reference_golden(name):
     douts = {f: g["dout_" + f] for f in parity.FN}
     got = parity.run_product(c, name=name, douts=douts)
     orc = parity.oracle_all(c, name=name, douts=douts)      # supplies the per-element scales and the cullable mass
-    worst = parity.assert_fields_and_grads(got, g, orc, (0, 1, 2, 3), name)
+    # per element and un-floored: 2e-5 (worst case over the goldens 1.2e-5, d2_degenerate_empty / third, at points that only see
+    # Gaussian tails: there |power| ~ 20 and ONE fp32 rounding of power — ulp(20) = 1.9e-6 — already moves exp(power) by
+    # 2e-6 relative; the reference's conic form and this library's whitened form round differently); normwise: 1e-5
+    worst = parity.assert_fields_and_grads(got, g, orc, (0, 1, 2, 3), name, fwd_rtol=2e-5)
+    for f in parity.FN:
+        assert worst["out_" + f][1] <= parity.FWD_RTOL, (name, f, worst["out_" + f])
     print(name, "worst per-element / normwise:", {k: (f"{a:.1e}", f"{b:.1e}") for k, (a, b) in worst.items()})
 
 

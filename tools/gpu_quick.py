@@ -62,7 +62,7 @@ def main():
         buf = ctypes.create_string_buffer(1 << 16)
         lib.dgs_profile_dump(buf, len(buf))
         lib.dgs_profile_enable(0)
-        rec["kernel_ms"] = {ln.split()[0]: round(float(ln.split()[1]), 4) for ln in buf.value.decode().splitlines() if ln.strip()}
+        rec["kernel_ms"] = {" ".join(ln.split()[:-2]): round(float(ln.split()[-2]), 4) for ln in buf.value.decode().splitlines() if ln.strip()}
     rec["pairs"] = dgs.count_pairs(gb, sb, nr, fn)
     rec["pairs_per_pt"] = rec["pairs"] / N
     rec["fwd_pairs_per_s"] = rec["pairs"] / (rec["t_fwd_ms"] * 1e-3)
