@@ -430,7 +430,7 @@ def run_ours(args, rank, world, local_rank):
         barrier()
     return dict(tot_ms=tot_ms, t_pre=t_pre, t_fwd=t_fwd, t_bwd=t_bwd, t_ar=t_ar, e2e=e2e, t_pre_reuse=t_pre_reuse, per_fn=per_fn,
                 clocks=clk, launches=launches, parity=parity,
-                N=N, P=P, D=D, C=C, fn=fn, state=state, dgs=dgs, lib=lib, _lib=_lib, bounds=bounds, host=host)
+                N=N, P=P, D=D, C=C, fn=fn, state=state, dgs=dgs, lib=lib, _lib=_lib, bounds=bounds, host=host, devt=devt)
 
 
 # ---------------------------------------------------------------------------------------
@@ -716,6 +716,11 @@ def main():
         dgs, lib, _lib = r["dgs"], r["lib"], r["_lib"]
         K = args.steps
         pairs = dgs.count_pairs(r["state"]["gb"], r["state"]["sb"], r["state"]["nr"], fn)
+        try:
+            pairs_sig = dgs.count_pairs(r["state"]["gb"], r["state"]["sb"], r["state"]["nr"], fn,
+                                        significant_for=(r["devt"]["means"], r["devt"]["conics"]))
+        except Exception:  # noqa: BLE001
+            pairs_sig = None
         peaks = measure_peaks(torch, lib, _lib)
         f_fwd, f_bwd = flops_per_pair(D, C, fn)
         bwd_ms, fwd_ms, pre_ms = med(r["t_bwd"]), med(r["t_fwd"]), med(r["t_pre"])
@@ -760,6 +765,7 @@ def main():
             "multi_gpu_parity": r["parity"],
             "fwd_bwd_only_points_per_s": N / ((fwd_ms + bwd_ms) * 1e-3),
             "pairs_evaluated_per_pass": pairs, "pairs_per_point": pairs / N,
+            "pairs_significant_per_pass": pairs_sig, "pairs_significant_per_point": (pairs_sig / N if pairs_sig else None),
             "gpu_launches": int(r["launches"]),
             "clocks": r["clocks"],
             "roofline": {"kernel": "dgs_backward_kernel", "bound": "fp32", "achieved": ach_bwd, "peak": peaks["fp32_tflops"],
@@ -769,9 +775,11 @@ def main():
                          "algorithmic_bytes": N * (4 * D + 4 + 4 * C) + P * 4 * (D + C + T),
                          "peak_source": "FFMA microbenchmark (dgs_microbench) measured in this run, burst",
                          "flop_per_pair": f_bwd, "launch_ms": bwd_ms,
+                         "frac_useful_pairs_only": (ach_bwd / peaks["fp32_tflops"] * pairs_sig / pairs if pairs_sig else None),
                          "sfu_frac": pairs / (bwd_ms * 1e-3) / 1e12 / peaks["ex2_tera_per_s"],
                          "forward": {"kernel": "dgs_forward_kernel", "achieved": ach_fwd, "frac": ach_fwd / peaks["fp32_tflops"],
                                      "flop_per_pair": f_fwd, "launch_ms": fwd_ms,
+                                     "frac_useful_pairs_only": (ach_fwd / peaks["fp32_tflops"] * pairs_sig / pairs if pairs_sig else None),
                                      "traffic": tr.get("dgs_forward_kernel") if tr_ok else None,
                                      "algorithmic_bytes": N * (4 * D + 4 + 4 * C),
                                      "sfu_frac": pairs / (fwd_ms * 1e-3) / 1e12 / peaks["ex2_tera_per_s"]},

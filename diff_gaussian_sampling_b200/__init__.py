@@ -644,13 +644,20 @@ def set_tuning(tile_target=0, fpc=0, T1=0):
     _lib.load().dgs_set_tuning(int(tile_target), int(fpc), int(T1))
 
 
-def count_pairs(binning_buffer, sample_binning_buffer, num_rendered, fn=0) -> int:
-    """(Gaussian, sample) pairs the accumulation kernels evaluate for function `fn` (roofline accounting)."""
+def count_pairs(binning_buffer, sample_binning_buffer, num_rendered, fn=0, significant_for=None) -> int:
+    """(Gaussian, sample) pairs the accumulation kernels evaluate for function `fn` (roofline accounting).
+    significant_for=(means, conics): only those with power >= -tau, i.e. the pairs that may not be skipped."""
     lib = _lib.load()
     plan = plan_of(binning_buffer, num_rendered)
     counter = torch.zeros(1, dtype=torch.int64, device=binning_buffer.device)
     with torch.cuda.device(binning_buffer.device):
         st = torch.cuda.current_stream().cuda_stream
-        _lib.check(lib.dgs_count_pairs(ctypes.byref(plan), fn, binning_buffer.data_ptr(), sample_binning_buffer.data_ptr(),
-                                       counter.data_ptr(), st), "dgs_count_pairs")
+        if significant_for is None:
+            _lib.check(lib.dgs_count_pairs(ctypes.byref(plan), fn, binning_buffer.data_ptr(), sample_binning_buffer.data_ptr(),
+                                           counter.data_ptr(), st), "dgs_count_pairs")
+        else:
+            means, conics = (_f32c(t, "means/conics") for t in significant_for)
+            _lib.check(lib.dgs_count_significant(ctypes.byref(plan), fn, means.data_ptr(), conics.data_ptr(),
+                                                 binning_buffer.data_ptr(), sample_binning_buffer.data_ptr(),
+                                                 counter.data_ptr(), st), "dgs_count_significant")
     return int(counter.item())

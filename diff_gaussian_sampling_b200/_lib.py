@@ -71,6 +71,7 @@ EXPORTS = {
                                                c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_microbench": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, ctypes.POINTER(ctypes.c_double), c_vp]),
     "dgs_count_pairs": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp]),
+    "dgs_count_significant": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_covariance_forward": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.c_int, c_vp, c_vp, c_vp]),
     "dgs_covariance_backward": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, ctypes.c_int, c_vp, c_vp, c_vp]),
     "dgs_aggregate_ws_bytes": (c_sz, [c_i64, ctypes.c_int]),

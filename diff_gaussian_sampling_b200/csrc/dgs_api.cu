@@ -156,7 +156,7 @@ static uint32_t higher_msb(uint32_t n) {
 
 // sample-side temporary region (inside the sample binning buffer, after the persistent arrays)
 struct SampleTmp {
-    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, l1_cnt, l1_start, l1_scan_tmp, total;
+    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, l1_cnt, l1_start, l1_scan_tmp, box_lo, box_hi, total;
 };
 static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
     SampleTmp t;
@@ -173,6 +173,9 @@ static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
     t.l1_cnt = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     t.l1_start = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     t.l1_scan_tmp = o; o = dgs_a128(o + dgs_scan_tmp_bytes((int64_t)pl->n_coarse + 1));
+    // ordered-int bounding boxes of the fine tiles (fused sample pass)
+    t.box_lo = o; o = dgs_a128(o + (size_t)pl->n_fine * 12);
+    t.box_hi = o; o = dgs_a128(o + (size_t)pl->n_fine * 12);
     t.total = o;
     return t;
 }
@@ -472,21 +475,49 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     uint32_t* rank_of = (uint32_t*)(stmp + tl.rank_of);
     if (!plan->samples_reused) {
         DGS_CUDA(cudaMemsetAsync(fine_start, 0, ((size_t)plan->n_fine + 1) * 4, st));
-        rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr, st);
-        if (rc) return rc;
-        rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
-        if (rc) return rc;
-        rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
-        if (rc) return rc;
-        rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
-        if (rc) return rc;
-        // public sorted sample list: stable sort on the cell bits == sort on bits [0, 32+bit)
-        rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(stmp + tl.alt_keys),
-                                (uint32_t*)(stmp + tl.alt_vals), N, 32, 32 + plan->sort_bits, stmp + tl.sort_tmp, st);
-        if (rc) return rc;
-        rc = dgs_launch_ranges(pa.keys, N, sample_ranges_dev, plan->n_ranges, st);
-        if (rc) return rc;
-
+        // fused sample pass: the cell bits fit one radix pass and every cell id is its own digit
+        const bool fused = plan->sort_bits >= 1 && plan->sort_bits <= 8 && plan->n_cells_ext <= (1 << plan->sort_bits);
+        if (fused) {
+            const int nd = 1 << plan->sort_bits;
+            const int n_chunks = dgs_cdiv(N, 2048);
+            uint32_t* hist = (uint32_t*)(stmp + tl.sort_tmp);
+            void* hist_scan_tmp = stmp + tl.sort_tmp + dgs_a128((size_t)256 * n_chunks * 4);
+            uint32_t* box_lo = (uint32_t*)(stmp + tl.box_lo);
+            uint32_t* box_hi = (uint32_t*)(stmp + tl.box_hi);
+            DGS_CUDA(cudaMemsetAsync(hist, 0, (size_t)nd * n_chunks * 4, st));
+            DGS_CUDA(cudaMemsetAsync(box_lo, 0xff, (size_t)plan->n_fine * 12, st));
+            DGS_CUDA(cudaMemsetAsync(box_hi, 0, (size_t)plan->n_fine * 12, st));
+            rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr,
+                                        hist, n_chunks, box_lo, box_hi, st);
+            if (rc) return rc;
+            rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
+            if (rc) return rc;
+            rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
+            if (rc) return rc;
+            rc = dgs_launch_tile_aabb_finalize(plan, box_lo, box_hi, fine_start, fine_aabb, coarse_aabb, st);
+            if (rc) return rc;
+            rc = dgs_sort_pairs_u64_prehist(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, N, 32, 32 + plan->sort_bits,
+                                            hist, hist_scan_tmp, st);
+            if (rc) return rc;
+            rc = dgs_launch_ranges_from_hist(hist, nd, n_chunks, N, sample_ranges_dev, plan->n_ranges, st);
+            if (rc) return rc;
+        } else {
+            rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr,
+                                        nullptr, 0, nullptr, nullptr, st);
+            if (rc) return rc;
+            rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
+            if (rc) return rc;
+            rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
+            if (rc) return rc;
+            rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
+            if (rc) return rc;
+            // public sorted sample list: stable sort on the cell bits == sort on bits [0, 32+bit)
+            rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(stmp + tl.alt_keys),
+                                    (uint32_t*)(stmp + tl.alt_vals), N, 32, 32 + plan->sort_bits, stmp + tl.sort_tmp, st);
+            if (rc) return rc;
+            rc = dgs_launch_ranges(pa.keys, N, sample_ranges_dev, plan->n_ranges, st);
+            if (rc) return rc;
+        }
     }
 
     // --- size of the coarse-tile lists: entries per tile (atomic counters), scanned into the list starts ---
@@ -644,6 +675,17 @@ extern "C" __attribute__((visibility("default"))) int dgs_count_pairs(const dgs_
     if (rc) return rc;
     return dgs_launch_forward(plan, fn, 1, nullptr, nullptr, nullptr, (uint8_t*)const_cast<void*>(binning_dev),
                               (const uint8_t*)sample_binning_dev, nullptr, nullptr, counter_dev, (cudaStream_t)stream);
+}
+
+int dgs_launch_count_significant(const dgs_plan_t* plan, int fn, const float* means, const float* conics, const uint8_t* gbuf,
+                                 const uint8_t* sbuf, unsigned long long* counter, cudaStream_t st);
+extern "C" __attribute__((visibility("default"))) int dgs_count_significant(const dgs_plan_t* plan, int fn, const float* means_dev, const float* conics_dev,
+                                     const void* binning_dev, const void* sample_binning_dev,
+                                     unsigned long long* counter_dev, void* stream) {
+    int rc = check_plan(plan);
+    if (rc) return rc;
+    return dgs_launch_count_significant(plan, fn, means_dev, conics_dev, (const uint8_t*)binning_dev,
+                                        (const uint8_t*)sample_binning_dev, counter_dev, (cudaStream_t)stream);
 }
 
 extern "C" __attribute__((visibility("default"))) size_t dgs_plan_sizeof(void) { return sizeof(dgs_plan_t); }

@@ -68,6 +68,7 @@ struct BwdArgs {
     int64_t N;
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
+    float t_max;                                  // tau of this function level x log2(e): |U X|^2 beyond it is culled
 };
 
 template <int D, int FN, int CB>
@@ -253,7 +254,7 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
 // staged samples.  FAST: whitened geometry without wrap; otherwise the literal reference pair.
 template <int D, int FN, int CB, int NG, bool FAST, bool VPOST>
 __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restrict__ sS, int np,
-                                          const uint32_t* __restrict__ queue, int count, int lane, const float* ctr) {
+                                          const uint32_t* __restrict__ queue, int count, int lane, const float* ctr, const float* hhalf) {
     using K = BwdCfg<D, FN, CB>;
     constexpr int T = K::T, U = K::U, SW = K::SW, SW0 = K::SW0, PO = K::PO;
     constexpr int PW = DGS_PREC_W(D);
@@ -331,6 +332,29 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
 #pragma unroll
         for (int k = 0; k < T; k++) { dC[0][k] = dC2[k].x; dC[1][k] = dC2[k].y; }
     } else {
+    // CENTRED (fn 0, fast path): second moments about the tile centre from the staged sample products.  Accumulating
+    // sum w x' x'^T in fp32 loses (|mu'| / |X|)^2 in relative precision (x' ~ mu' when the tile is much wider than the
+    // Gaussian's reach), so a batch takes this form only if the tile's half diagonal lies within 1.5x the tau ellipsoid
+    // of EVERY Gaussian of the batch (measured in the whitened metric); otherwise the per-pair products w X_i X_j.
+    bool centred_ok = false;
+    if constexpr (FN == 0 && FAST) {
+        bool ok = true;
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            float th = 0.f;
+#pragma unroll
+            for (int i = 0; i < D; i++) {
+                float y = 0.f;
+#pragma unroll
+                for (int j = i; j < D; j++) y = fmaf(fabsf(geo[g][dgs_tri(D, i, j)]), hhalf[j], y);
+                th = fmaf(y, y, th);
+            }
+            ok = ok && (!valid[g] || th <= 2.25f * A.t_max);
+        }
+        centred_ok = __all_sync(0xffffffffu, ok);
+    }
+    auto run_samples = [&](auto centred_tag) {
+    constexpr bool CENTRED = decltype(centred_tag)::value != 0;
 #pragma unroll 2
     for (int s = 0; s < np; s++) {
         float sr[SW];
@@ -382,7 +406,7 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
                     }
                     w = Gv * S;
                 }
-                if (FAST) {
+                if (CENTRED) {
                     // first moment about the mean from the displacement at hand, second moment about the tile centre
                     // from the sample's own products (converted after the loop): D + T FFMA per pair
 #pragma unroll
@@ -408,8 +432,13 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
             }
         }
     }
-    }   // scalar path
-    if constexpr (FN == 0 && FAST && !(BWD_PACKED && VPOST && NG == 2 && CB == 1)) {
+    };
+    if constexpr (FN == 0 && FAST) {
+        if (centred_ok) run_samples(DgsInt<1>{}); else run_samples(DgsInt<0>{});
+    } else {
+        run_samples(DgsInt<0>{});
+    }
+    if (centred_ok) {
         // sum w X X^T = S2' + mu' m1^T + m1 mu'^T - mu' mu'^T W,  S2' = sum w x' x'^T, mu' = mu - centre, m1 = sum w X, W = sum w
 #pragma unroll
         for (int g = 0; g < NG; g++) {
@@ -434,6 +463,7 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
                 }
         }
     }
+    }   // scalar path
     if constexpr (MOMENTS) {
 #pragma unroll
         for (int g = 0; g < NG; g++) {
@@ -495,9 +525,9 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
             const float4 b1 = *(const float4*)(A.fine_aabb + tile * 8 + 4);
             lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b0.w; hi[1] = b1.x; hi[2] = b1.y;
         }
-        float ctr[3];
+        float ctr[3], hhalf[3];
 #pragma unroll
-        for (int d = 0; d < 3; d++) ctr[d] = 0.5f * (lo[d] + hi[d]);
+        for (int d = 0; d < 3; d++) { ctr[d] = 0.5f * (lo[d] + hi[d]); hhalf[d] = 0.5f * (hi[d] - lo[d]); }
 
         const uint32_t n = s1 - s0;
         const uint32_t n_pass = (n + SCAP - 1) / SCAP;
@@ -600,7 +630,7 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     nq = remq;
                     __syncwarp();
                     if (nf >= 32 * NG) {
-                        bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane, ctr);
+                        bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane, ctr, hhalf);
                         const int rem = nf - 32 * NG;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qF[32 * NG + lane];
@@ -610,7 +640,7 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         __syncwarp();
                     }
                     if (ng >= 32) {
-                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, 32, lane, ctr);
+                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, 32, lane, ctr, hhalf);
                         const int rem = ng - 32;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qG[32 + lane];
@@ -625,10 +655,10 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     // leftovers (nf < 32 * NG, ng < 32) are processed here unconditionally: ids queued by an earlier
                     // drain must not depend on a later chunk of the list having a survivor for this tile
                     if (nf > 0) {
-                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane, ctr);
-                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane, ctr);
+                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane, ctr, hhalf);
+                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane, ctr, hhalf);
                     }
-                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, ng, lane, ctr);
+                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, ng, lane, ctr, hhalf);
                     break;
                 }
             }
@@ -744,6 +774,7 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
     a.sched = (uint32_t*)(gbuf + plan->g_sched_off) + 1;     // the forward's counter is word 0
     a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
+    a.t_max = dgs_tau_for(plan, dgs_mask_level(fn)) * 1.44269504088896340736f;
     const int T = plan->D * (plan->D + 1) / 2;
     // the kernels accumulate: start from zero whatever the caller left in the buffers
     DGS_CUDA(cudaMemsetAsync(dmeans, 0, (size_t)plan->P * plan->D * 4, st));

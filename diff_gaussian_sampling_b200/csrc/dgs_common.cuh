@@ -96,9 +96,32 @@ size_t dgs_sort_tmp_bytes(int64_t n);
 int dgs_sort_pairs_u64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                        uint64_t* keys_alt, uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit, void* tmp,
                        cudaStream_t st);
+int dgs_sort_pairs_u64_prehist(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                               int64_t n, int begin_bit, int end_bit, uint32_t* hist, void* scan_tmp, cudaStream_t st);
 int dgs_sort_pairs_u32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out,
                        uint32_t* keys_alt, uint32_t* vals_alt, int64_t n, int begin_bit, int end_bit, void* tmp,
                        cudaStream_t st);
+
+// Lanes of the warp whose 8-bit digit equals this lane's (invalid lanes match nobody).  EMULATE: eight ballots instead of
+// the MATCH instruction — measured on B200 (profiles/r02_match_emulation.jsonl): faster inside the per-tile list sort
+// (0.162 -> 0.115 ms at cfg2: short dependent rounds, MATCH latency exposed), slower in the device-wide radix passes
+// (0.245 -> 0.282 ms: throughput-bound, 8 ballots cost more issue slots), so each user picks its own.
+#ifdef __CUDACC__
+template <bool EMULATE>
+__device__ __forceinline__ uint32_t dgs_match_digit8(uint32_t d, bool valid) {
+    if (EMULATE) {
+        uint32_t m = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t b = __ballot_sync(0xffffffffu, (d >> k) & 1u);
+            m &= ((d >> k) & 1u) ? b : ~b;
+        }
+        return valid ? m : 0u;
+    }
+    const uint32_t peers = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
+    return valid ? peers : 0u;
+}
+#endif
 
 #define DGS_FN_JET 4   // function code of the fused value + derivative + Hessian traversal (dgs_field.cuh)
 

@@ -19,6 +19,7 @@
 // candidates.  Gaussians that need the torus wrap for some sample of the tile, or whose conic
 // is not positive definite, take the "general" path that restates forward.cu:147-184 literally.
 // Bound: FP32 pipe and MUFU.EX2 (8 lane-cycles each per pair and SM sub-partition in 2D).
+#include <string.h>
 #include "dgs_field.cuh"
 #include "dgs_math.cuh"
 
@@ -610,6 +611,71 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     if (plan->D == 1) fwd_launch_d<1>(a, fn, st);
     else if (plan->D == 2) fwd_launch_d<2>(a, fn, st);
     else fwd_launch_d<3>(a, fn, st);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+
+// ---------------------------------------------------------------------------------------
+// Diagnostic (roofline accounting): of the pairs the accumulation kernels evaluate for function level `fn`, how many
+// have power >= -tau, i.e. are NOT skippable.  Plain kernel: one warp per fine tile, lanes over samples, literal pair
+// arithmetic (forward.cu:147-184).  Not on any hot path.
+// ---------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(128) dgs_count_significant_kernel(const FwdArgs A, const float* __restrict__ means,
+                                                                    float g_min) {
+    constexpr int T = D * (D + 1) / 2;
+    const int lane = threadIdx.x & 31;
+    const int64_t tile = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (tile >= (int64_t)A.n_tiles) return;
+    const int64_t coarse = tile / A.fpcD;
+    const int ft = (int)(tile - coarse * A.fpcD);
+    const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
+    const uint32_t g0 = A.l1_start[coarse], g1 = A.l1_start[coarse + 1];
+    unsigned long long n = 0;
+    for (uint32_t e = g0; e < g1; e++) {
+        if (!dgs_mask_bit(A.mask, A.mask64, e, ft)) continue;
+        const uint32_t id = A.l1_ids[e];
+        float mu[D], con[T];
+#pragma unroll
+        for (int d = 0; d < D; d++) mu[d] = means[(int64_t)id * D + d];
+#pragma unroll
+        for (int k = 0; k < T; k++) con[k] = A.conics[(int64_t)id * T + k];
+        for (uint32_t j = s0 + lane; j < s1; j += 32) {
+            float x[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) x[d] = A.fine_xyz[(int64_t)d * A.N + j];
+            DgsPair<D, 0, true> p;
+            p.eval(x, mu, con);
+            n += (p.G >= g_min) ? 1ull : 0ull;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if (lane == 0 && n) atomicAdd(A.pair_counter, n);
+}
+
+int dgs_launch_count_significant(const dgs_plan_t* plan, int fn, const float* means, const float* conics, const uint8_t* gbuf,
+                                 const uint8_t* sbuf, unsigned long long* counter, cudaStream_t st) {
+    if (plan->N <= 0 || plan->n_coarse <= 0 || plan->P <= 0) return 0;
+    FwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.conics = conics;
+    a.mask64 = plan->mask_bytes == 8 ? 1 : 0;
+    a.mask = gbuf + plan->g_l1_mask_off + (size_t)dgs_mask_level(fn) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
+    a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
+    a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
+    a.fine_start = (const uint32_t*)(sbuf + plan->s_fine_start_off);
+    a.fine_xyz = (const float*)(sbuf + plan->s_fine_xyz_off);
+    a.pair_counter = counter;
+    a.N = plan->N; a.fpcD = plan->fine_per_coarse;
+    a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
+    const float g_min = expf(-dgs_tau_for(plan, dgs_mask_level(fn)));
+    const int nb = dgs_cdiv((int64_t)a.n_tiles, 4);
+    if (plan->D == 1) dgs_count_significant_kernel<1><<<nb, 128, 0, st>>>(a, means, g_min);
+    else if (plan->D == 2) dgs_count_significant_kernel<2><<<nb, 128, 0, st>>>(a, means, g_min);
+    else dgs_count_significant_kernel<3><<<nb, 128, 0, st>>>(a, means, g_min);
+    DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
 }

@@ -27,10 +27,11 @@ __global__ void dgs_header_init_kernel(DgsDevHeader* h) {
 }
 
 template <int D>
-__global__ void __launch_bounds__(DGS_THREADS) dgs_bounds_kernel(const float* __restrict__ samples, int64_t n_flat, DgsDevHeader* h) {
+__global__ void __launch_bounds__(DGS_THREADS) dgs_bounds_kernel(const float* __restrict__ samples, int64_t n_flat, DgsDevHeader* h,
+                                                                 int64_t stride_mul = 1) {
     // gridDim.x is a multiple of 3, so the flat stride is a multiple of D and each thread
     // stays on one axis; consecutive threads read consecutive floats.
-    const int64_t stride = (int64_t)gridDim.x * DGS_THREADS;
+    const int64_t stride = (int64_t)gridDim.x * DGS_THREADS * stride_mul;
     const int64_t t = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
     const int axis = (int)(t % D);
     float lo = INFINITY, hi = -INFINITY;
@@ -62,9 +63,22 @@ __global__ void dgs_bounds_finalize_kernel(DgsDevHeader* h, int D) {
 
 int dgs_launch_bounds(const float* samples, int64_t N, int D, DgsDevHeader* h, bool finalize, cudaStream_t st) {
     DGS_PROF("bounds", st);
-    const int64_t n_flat = N * D;
-    int nb = dgs_cdiv(n_flat, (int64_t)DGS_THREADS * 8);
+    int64_t n_flat = N * D;
+    // Without `finalize` the caller supplied the bounds and the reduction only ESTIMATES the extent of this call's samples
+    // (tile sizing of a point shard; results do not depend on it): a prefix-strided subset of about 1.5M values is enough.
+    int64_t stride_mul = 1;
+    if (!finalize && n_flat > (int64_t)3 << 19) stride_mul = n_flat / ((int64_t)3 << 19);
+    int nb = dgs_cdiv(n_flat / stride_mul, (int64_t)DGS_THREADS * 8);
     nb = nb < 3 ? 3 : (nb > 148 * 12 ? 148 * 12 : ((nb + 2) / 3) * 3);
+    if (stride_mul > 1) {
+        // every thread walks i = t, t + stride, ... with stride = grid size x stride_mul (still a multiple of D)
+        if (D == 1) dgs_bounds_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h, stride_mul);
+        else if (D == 2) dgs_bounds_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h, stride_mul);
+        else dgs_bounds_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h, stride_mul);
+        DGS_NOTE_LAUNCHES(1);
+        DGS_LAUNCH_CHECK();
+        return 0;
+    }
     if (D == 1) dgs_bounds_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
     else if (D == 2) dgs_bounds_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
     else dgs_bounds_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, n_flat, h);
@@ -375,15 +389,23 @@ static DgsTiles make_tiles(const dgs_plan_t* plan) {
     return t;
 }
 
-// sampleWithKeys (sampler_impl.cu:155-189) + fine-tile id and rank of every sample.
-template <int D>
+// sampleWithKeys (sampler_impl.cu:155-189) + fine-tile id and rank of every sample.  FUSED (the cell bits fit one radix
+// pass and every cell id is its own digit): the kernel also builds (i) the per-chunk cell histogram of the public key
+// sort, so that the sort needs no counting pass and the sample ranges fall out of its scan, and (ii) the bounding boxes
+// of the samples of every fine tile with ordered-int atomics (warp-aggregated per tile), so that no pass re-reads the
+// coordinates for them.
+#define DGS_SORT_CHUNK 2048     // == SORT_CHUNK of dgs_scan_sort.cu (checked there)
+template <int D, bool FUSED>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_sample_keys_kernel(const float* __restrict__ samples, int64_t N, DgsTiles G,
                                                                       uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
                                                                       uint32_t* __restrict__ tile_of, uint32_t* __restrict__ rank_of,
-                                                                      uint32_t* __restrict__ fine_cnt, DgsDevHeader* __restrict__ h) {
+                                                                      uint32_t* __restrict__ fine_cnt, DgsDevHeader* __restrict__ h,
+                                                                      uint32_t* __restrict__ cell_hist, int n_chunks,
+                                                                      uint32_t* __restrict__ box_lo, uint32_t* __restrict__ box_hi) {
     const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
     const bool valid = i < N;
-    uint32_t tile = 0xffffffffu;
+    uint32_t tile = 0xffffffffu, cell = 0xffffffffu;
+    float sv[3] = {0.f, 0.f, 0.f};
     if (valid) {
         uint32_t c[3] = {0, 0, 0};
         int f[3] = {0, 0, 0};
@@ -391,13 +413,14 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_sample_keys_kernel(const floa
 #pragma unroll
         for (int d = 0; d < D; d++) {
             const float s = samples[i * D + d];
+            sv[d] = s;
             float q;
             const int cd = dgs_sample_cell(s, G.off[d], G.g[d], &q);
             c[d] = (uint32_t)cd;
             f[d] = dgs_fine_coord(q, cd, G.F);
             outside = outside || !(s >= G.off[d] && s <= G.hi[d]);
         }
-        uint32_t cell = c[0];
+        cell = c[0];
         if (D > 1) cell += c[1] * (uint32_t)G.g[0];
         if (D > 2) cell += c[2] * (uint32_t)G.g[1] * (uint32_t)G.g[0];
         uint64_t key = cell;
@@ -414,15 +437,38 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_sample_keys_kernel(const floa
         tile = (cell * (uint32_t)G.cpc + csub) * (uint32_t)G.fpcD + fsub;
         if (outside) atomicOr(&h->flags, DGS_HDR_OUTSIDE);
     }
+    const int lane = threadIdx.x & 31;
     const uint32_t peers = __match_any_sync(0xffffffffu, tile);
+    const int leader = __ffs(peers) - 1;
     if (valid) {
-        const int lane = threadIdx.x & 31;
-        const int leader = __ffs(peers) - 1;
         uint32_t base = 0;
         if (lane == leader) base = atomicAdd(&fine_cnt[tile], (uint32_t)__popc(peers));
         base = __shfl_sync(peers, base, leader);
         tile_of[i] = tile;
         rank_of[i] = base + __popc(peers & ((1u << lane) - 1u));
+    }
+    if (FUSED) {
+        // bounding box of the tile's samples: warp-aggregated over the lanes of the same tile
+        if (valid) {
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const uint32_t o = dgs_f2ord(sv[d]);
+                const uint32_t mn = __reduce_min_sync(peers, o), mx = __reduce_max_sync(peers, o);
+                if (lane == leader) {
+                    atomicMin(&box_lo[(int64_t)tile * 3 + d], mn);
+                    atomicMax(&box_hi[(int64_t)tile * 3 + d], mx);
+                }
+            }
+        }
+        // histogram of the cell digit per sort chunk (a warp lies inside one chunk; mostly one cell per warp)
+        const uint32_t cell0 = __shfl_sync(0xffffffffu, cell, 0);
+        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        const int64_t chunk = ((int64_t)blockIdx.x * DGS_THREADS + (threadIdx.x & ~31)) / DGS_SORT_CHUNK;
+        if (__all_sync(0xffffffffu, !valid || cell == cell0)) {
+            if (lane == 0 && vmask) atomicAdd(&cell_hist[(int64_t)cell0 * n_chunks + chunk], (uint32_t)__popc(vmask));
+        } else if (valid) {
+            atomicAdd(&cell_hist[(int64_t)cell * n_chunks + chunk], 1u);
+        }
     }
 }
 
@@ -500,15 +546,95 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float*
 }
 
 int dgs_launch_sample_keys(const float* samples, const dgs_plan_t* plan, uint64_t* keys, uint32_t* vals, uint32_t* tile_of,
-                           uint32_t* rank_of, uint32_t* fine_cnt, DgsDevHeader* h, cudaStream_t st) {
+                           uint32_t* rank_of, uint32_t* fine_cnt, DgsDevHeader* h, uint32_t* cell_hist, int n_chunks,
+                           uint32_t* box_lo, uint32_t* box_hi, cudaStream_t st) {
     DGS_PROF("sample_keys", st);
     const int64_t N = plan->N;
     if (N <= 0) return 0;
     DgsTiles G = make_tiles(plan);
     const int nb = dgs_cdiv(N, DGS_THREADS);
-    if (plan->D == 1) dgs_sample_keys_kernel<1><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
-    else if (plan->D == 2) dgs_sample_keys_kernel<2><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
-    else dgs_sample_keys_kernel<3><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h);
+#define SK_LAUNCH(DD)                                                                                                              \
+    if (cell_hist) dgs_sample_keys_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h, cell_hist, n_chunks, box_lo, box_hi); \
+    else dgs_sample_keys_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(samples, N, G, keys, vals, tile_of, rank_of, fine_cnt, h, nullptr, 0, nullptr, nullptr);
+    if (plan->D == 1) { SK_LAUNCH(1) } else if (plan->D == 2) { SK_LAUNCH(2) } else { SK_LAUNCH(3) }
+#undef SK_LAUNCH
+    DGS_NOTE_LAUNCHES(1);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// Fused path: ordered-int boxes + counts -> the float boxes of the fine tiles and their union per coarse tile.
+// One warp per coarse tile.
+__global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_finalize_kernel(const uint32_t* __restrict__ box_lo,
+                                                                             const uint32_t* __restrict__ box_hi,
+                                                                             const uint32_t* __restrict__ fine_start, int fpcD,
+                                                                             int n_coarse, float* __restrict__ fine_aabb,
+                                                                             float* __restrict__ coarse_aabb) {
+    const int lane = threadIdx.x & 31;
+    const int64_t coarse = (int64_t)blockIdx.x * (DGS_THREADS / 32) + (threadIdx.x >> 5);
+    if (coarse >= n_coarse) return;
+    float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    uint32_t cn = 0;
+    for (int ft = lane; ft < fpcD; ft += 32) {
+        const int64_t tile = coarse * fpcD + ft;
+        const uint32_t n = fine_start[tile + 1] - fine_start[tile];
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        if (n) {
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const uint32_t l = box_lo[tile * 3 + d], u = box_hi[tile * 3 + d];
+                if (l <= u && l != 0xffffffffu) { lo[d] = dgs_ord2f(l); hi[d] = dgs_ord2f(u); }
+                clo[d] = fminf(clo[d], lo[d]);
+                chi[d] = fmaxf(chi[d], hi[d]);
+            }
+        }
+        cn += n;
+        float* o = fine_aabb + tile * 8;
+        o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2]; o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
+        o[6] = __int_as_float((int)n); o[7] = 0.f;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            clo[d] = fminf(clo[d], __shfl_xor_sync(0xffffffffu, clo[d], o));
+            chi[d] = fmaxf(chi[d], __shfl_xor_sync(0xffffffffu, chi[d], o));
+        }
+        cn += __shfl_xor_sync(0xffffffffu, cn, o);
+    }
+    if (lane == 0) {
+        float* o = coarse_aabb + coarse * 8;
+        o[0] = clo[0]; o[1] = clo[1]; o[2] = clo[2]; o[3] = chi[0]; o[4] = chi[1]; o[5] = chi[2];
+        o[6] = __int_as_float((int)cn); o[7] = 0.f;
+    }
+}
+
+int dgs_launch_tile_aabb_finalize(const dgs_plan_t* plan, const uint32_t* box_lo, const uint32_t* box_hi, const uint32_t* fine_start,
+                                  float* fine_aabb, float* coarse_aabb, cudaStream_t st) {
+    DGS_PROF("tile_aabb_finalize", st);
+    if (plan->n_coarse <= 0) return 0;
+    dgs_tile_aabb_finalize_kernel<<<dgs_cdiv(plan->n_coarse, DGS_THREADS / 32), DGS_THREADS, 0, st>>>(
+        box_lo, box_hi, fine_start, plan->fine_per_coarse, plan->n_coarse, fine_aabb, coarse_aabb);
+    DGS_NOTE_LAUNCHES(1);
+    DGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// Fused path: sample_ranges straight from the scanned per-chunk cell histogram (digit d == cell d): cell d holds the
+// sorted positions [hist[d][0], hist[d + 1][0]); empty cells keep the caller's zero fill (sampler_impl.cu:141-150).
+__global__ void dgs_ranges_from_hist_kernel(const uint32_t* __restrict__ hist_scanned, int nd, int n_chunks, uint32_t total,
+                                            uint2* __restrict__ ranges, int n_ranges) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= nd || d >= n_ranges) return;
+    const uint32_t a = hist_scanned[(int64_t)d * n_chunks];
+    const uint32_t b = (d + 1 < nd) ? hist_scanned[(int64_t)(d + 1) * n_chunks] : total;
+    if (b > a) ranges[d] = make_uint2(a, b);
+}
+
+int dgs_launch_ranges_from_hist(const uint32_t* hist_scanned, int nd, int n_chunks, int64_t total, void* ranges, int n_ranges,
+                                cudaStream_t st) {
+    DGS_PROF("ranges_from_hist", st);
+    dgs_ranges_from_hist_kernel<<<dgs_cdiv(nd, 128), 128, 0, st>>>(hist_scanned, nd, n_chunks, (uint32_t)total, (uint2*)ranges, n_ranges);
     DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
@@ -727,8 +853,8 @@ __device__ __forceinline__ void l1s_pass(const uint32_t* A, uint32_t* B, uint32_
     for (uint32_t b = s0; b < s1; b += 32) {
         const uint32_t i = b + lane;
         const bool valid = i < s1;
-        const uint32_t d = valid ? ((A[i] >> shift) & 255u) : 0xffffffffu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t d = valid ? ((A[i] >> shift) & 255u) : 0u;
+        const uint32_t peers = dgs_match_digit8<true>(d, valid);
         if (valid && lane == __ffs(peers) - 1) hist[w][d] += __popc(peers);
         __syncwarp();
     }
@@ -760,9 +886,9 @@ __device__ __forceinline__ void l1s_pass(const uint32_t* A, uint32_t* B, uint32_
         const uint32_t i = b + lane;
         const bool valid = i < s1;
         const uint32_t key = valid ? A[i] : 0u;
-        const uint32_t d = valid ? ((key >> shift) & 255u) : 0xffffffffu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(peers) - 1;
+        const uint32_t d = valid ? ((key >> shift) & 255u) : 0u;
+        const uint32_t peers = dgs_match_digit8<true>(d, valid);
+        const int leader = valid ? __ffs(peers) - 1 : lane;
         uint32_t old = 0;
         if (valid && lane == leader) { old = hist[w][d]; hist[w][d] = old + __popc(peers); }
         __syncwarp();

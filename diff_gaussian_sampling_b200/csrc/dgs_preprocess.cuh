@@ -13,7 +13,12 @@ int dgs_launch_duplicate(const float* means, const float* radii, const uint32_t*
                          const dgs_plan_t* plan, uint64_t* keys, uint32_t* vals, cudaStream_t st);
 int dgs_launch_ranges(const uint64_t* keys, int64_t L, void* ranges, int n_ranges, cudaStream_t st);
 int dgs_launch_sample_keys(const float* samples, const dgs_plan_t* plan, uint64_t* keys, uint32_t* vals, uint32_t* tile_of,
-                           uint32_t* rank_of, uint32_t* fine_cnt, DgsDevHeader* h, cudaStream_t st);
+                           uint32_t* rank_of, uint32_t* fine_cnt, DgsDevHeader* h, uint32_t* cell_hist, int n_chunks,
+                           uint32_t* box_lo, uint32_t* box_hi, cudaStream_t st);
+int dgs_launch_tile_aabb_finalize(const dgs_plan_t* plan, const uint32_t* box_lo, const uint32_t* box_hi, const uint32_t* fine_start,
+                                  float* fine_aabb, float* coarse_aabb, cudaStream_t st);
+int dgs_launch_ranges_from_hist(const uint32_t* hist_scanned, int nd, int n_chunks, int64_t total, void* ranges, int n_ranges,
+                                cudaStream_t st);
 int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const uint32_t* tile_of, const uint32_t* rank_of,
                             const uint32_t* fine_start, uint32_t* fine_ids, float* fine_xyz, cudaStream_t st);
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,

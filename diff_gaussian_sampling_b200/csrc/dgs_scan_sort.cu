@@ -156,10 +156,10 @@ __device__ __forceinline__ void radix_rank_chunk(const K* __restrict__ keys, int
         const int64_t i = base + k * 32;
         const bool valid = i < n;
         key[k] = valid ? keys[i] : (K)0;
-        const uint32_t d = valid ? (uint32_t)((key[k] >> shift) & (K)mask) : 0xffffffffu;
+        const uint32_t d = valid ? (uint32_t)((key[k] >> shift) & (K)mask) : 0u;
         dig[k] = d;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(peers) - 1;
+        const uint32_t peers = dgs_match_digit8<false>(d, valid);
+        const int leader = valid ? __ffs(peers) - 1 : lane;
         const uint32_t below = __popc(peers & ((1u << lane) - 1u));
         uint32_t old = 0;
         if (lane == leader && valid) {
@@ -273,6 +273,27 @@ static int sort_impl(const K* keys_in, const uint32_t* vals_in, K* keys_out, uin
         src_k = dst_k;
         src_v = dst_v;
     }
+    return 0;
+}
+
+// One-pass variant whose per-chunk digit histogram `hist` ([digit][chunk], n_chunks = ceil(n / 2048)) was already built by
+// the kernel that produced the keys: scan + scatter only.  hist is scanned in place (its first column then holds the
+// start of every digit).  bits = end_bit - begin_bit <= 8.
+static_assert(SORT_CHUNK == 2048, "DGS_SORT_CHUNK in dgs_preprocess.cu assumes 2048");
+int dgs_sort_pairs_u64_prehist(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                               int64_t n, int begin_bit, int end_bit, uint32_t* hist, void* scan_tmp, cudaStream_t st) {
+    DGS_PROF("radix_sort_u64_prehist(scan+scatter)", st);
+    if (n <= 0) return 0;
+    const int nbits = end_bit - begin_bit;
+    DGS_REQUIRE(nbits >= 1 && nbits <= 8, DGS_ERR_BAD_ARG, "prehist sort needs 1..8 bits");
+    const int nd = 1 << nbits;
+    const int n_chunks = dgs_cdiv(n, SORT_CHUNK);
+    int rc = dgs_exclusive_scan_u32(hist, hist, (int64_t)nd * n_chunks, scan_tmp, nullptr, st);
+    if (rc) return rc;
+    radix_scatter_kernel<uint64_t><<<n_chunks, DGS_THREADS, 0, st>>>(keys_in, vals_in, keys_out, vals_out, n, begin_bit,
+                                                                      (uint32_t)nd - 1u, nd, n_chunks, hist);
+    DGS_NOTE_LAUNCHES(1);
+    DGS_LAUNCH_CHECK();
     return 0;
 }
 

@@ -248,6 +248,12 @@ int dgs_sample_jet_backward(const dgs_plan_t* plan, int C,
 int dgs_count_pairs(const dgs_plan_t* plan, int fn, const void* binning_dev, const void* sample_binning_dev,
                     unsigned long long* counter_dev, void* stream);
 
+/* Of those, the pairs with power >= -tau of the function level (the ones that may NOT be skipped): the "useful" part of
+ * pairs_evaluated in the roofline accounting.  Diagnostic kernel (literal pair arithmetic), not on a hot path. */
+int dgs_count_significant(const dgs_plan_t* plan, int fn, const float* means_dev, const float* conics_dev,
+                          const void* binning_dev, const void* sample_binning_dev,
+                          unsigned long long* counter_dev, void* stream);
+
 /*
  * ---- aggregate_neighbors (reference: aggregate_neighbors.cu / aggregate_neighbors.h:11-47) ----
  * preprocess_aggregate is two-phase because the CSR length is data dependent (the reference
