@@ -156,7 +156,7 @@ static uint32_t higher_msb(uint32_t n) {
 
 // sample-side temporary region (inside the sample binning buffer, after the persistent arrays)
 struct SampleTmp {
-    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, l1_cnt, l1_start, l1_scan_tmp, box_lo, box_hi, total;
+    size_t tile_of, rank_of, sort_tmp, scan_tmp, alt_keys, alt_vals, l1_cnt, l1_start, l1_scan_tmp, box_lo, box_hi, sranges, total;
 };
 static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
     SampleTmp t;
@@ -176,6 +176,7 @@ static SampleTmp sample_tmp_layout(const dgs_plan_t* pl) {
     // ordered-int bounding boxes of the fine tiles (fused sample pass)
     t.box_lo = o; o = dgs_a128(o + (size_t)pl->n_fine * 12);
     t.box_hi = o; o = dgs_a128(o + (size_t)pl->n_fine * 12);
+    t.sranges = o; o = dgs_a128(o + (size_t)pl->ranges_bytes);      // copy of sample_ranges for the two list-build passes
     t.total = o;
     return t;
 }
@@ -388,6 +389,13 @@ extern "C" __attribute__((visibility("default"))) int dgs_plan_begin(const float
     if (D > 2) ext_cells += (int64_t)plan->grid[2] * plan->grid[1] * plan->grid[0];
     plan->n_cells_ext = (int)(ext_cells + 1);
     plan->mean_extent = h.extent_cnt ? (float)(h.extent_sum / (double)h.extent_cnt) : 0.f;
+    {
+        const uint32_t u = h.min_reach_bits;
+        uint32_t b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+        float f;
+        memcpy(&f, &b, 4);
+        plan->min_reach = (u != 0xffffffffu && isfinite(f) && f > 0.f) ? f : 0.f;
+    }
     // fraction of the bounding box that this call's samples span (1 unless the caller supplied wider, global bounds)
     double occupied = 1.0;
     for (int d = 0; d < D; d++) {
@@ -482,19 +490,18 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
             const int n_chunks = dgs_cdiv(N, 2048);
             uint32_t* hist = (uint32_t*)(stmp + tl.sort_tmp);
             void* hist_scan_tmp = stmp + tl.sort_tmp + dgs_a128((size_t)256 * n_chunks * 4);
-            uint32_t* box_lo = (uint32_t*)(stmp + tl.box_lo);
-            uint32_t* box_hi = (uint32_t*)(stmp + tl.box_hi);
+            // The tile boxes stay a separate pass over the re-ordered coordinates: warp-aggregated ordered-int atomics
+            // inside the key kernel were measured SLOWER (sample_keys 0.117 -> 0.199 ms in 2D, 0.141 -> 0.467 ms in 3D,
+            // against 0.052 / 0.090 ms for dgs_tile_aabb_kernel; profiles/r02_quick_g_*.json).
             DGS_CUDA(cudaMemsetAsync(hist, 0, (size_t)nd * n_chunks * 4, st));
-            DGS_CUDA(cudaMemsetAsync(box_lo, 0xff, (size_t)plan->n_fine * 12, st));
-            DGS_CUDA(cudaMemsetAsync(box_hi, 0, (size_t)plan->n_fine * 12, st));
             rc = dgs_launch_sample_keys(samples_dev, plan, pa.keys_unsorted, pa.list_unsorted, tile_of, rank_of, fine_start, hdr,
-                                        hist, n_chunks, box_lo, box_hi, st);
+                                        hist, n_chunks, nullptr, nullptr, st);
             if (rc) return rc;
             rc = dgs_exclusive_scan_u32(fine_start, fine_start, (int64_t)plan->n_fine + 1, stmp + tl.scan_tmp, nullptr, st);
             if (rc) return rc;
             rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
             if (rc) return rc;
-            rc = dgs_launch_tile_aabb_finalize(plan, box_lo, box_hi, fine_start, fine_aabb, coarse_aabb, st);
+            rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
             if (rc) return rc;
             rc = dgs_sort_pairs_u64_prehist(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, N, 32, 32 + plan->sort_bits,
                                             hist, hist_scan_tmp, st);
@@ -524,7 +531,8 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     uint32_t* l1_cnt = (uint32_t*)(stmp + tl.l1_cnt);
     uint32_t* l1_start_tmp = (uint32_t*)(stmp + tl.l1_start);
     DGS_CUDA(cudaMemsetAsync(l1_cnt, 0, ((size_t)plan->n_coarse + 1) * 4, st));
-    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, l1_cnt,
+    DGS_CUDA(cudaMemcpyAsync(stmp + tl.sranges, sample_ranges_dev, (size_t)plan->ranges_bytes, cudaMemcpyDeviceToDevice, st));
+    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, stmp + tl.sranges, l1_cnt,
                        (unsigned long long*)(g + gl.n1bits), nullptr, st);
     if (rc) return rc;
     rc = dgs_exclusive_scan_u32(l1_cnt, l1_start_tmp, (int64_t)plan->n_coarse + 1, stmp + tl.l1_scan_tmp, (uint32_t*)&hdr->n_l1, st);
@@ -585,7 +593,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     rc = dgs_launch_l1_cursor_init((const uint32_t*)(stmp + stl.l1_start), plan->n_coarse + 1, l1_start, cursor, st);
     if (rc) return rc;
     if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, cursor,
+        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, stmp + stl.sranges, cursor,
                            (unsigned long long*)(g + gl.n1bits), l1_ids, st);
         if (rc) return rc;
         rc = dgs_launch_l1_sort(plan, l1_start, l1_ids, (uint32_t*)(tmp + tl.l1_alt), st);

@@ -69,6 +69,7 @@ struct BwdArgs {
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
     float t_max;                                  // tau of this function level x log2(e): |U X|^2 beyond it is culled
+    int centred;                                  // fn 0: second moments about the tile centre are numerically safe (launcher)
 };
 
 template <int D, int FN, int CB>
@@ -252,7 +253,7 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
 
 // One batch: every lane owns NG Gaussians (queue entries lane, lane+32, ...) and walks the np
 // staged samples.  FAST: whitened geometry without wrap; otherwise the literal reference pair.
-template <int D, int FN, int CB, int NG, bool FAST, bool VPOST>
+template <int D, int FN, int CB, int NG, bool FAST, bool VPOST, bool CENTRED_K>
 __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restrict__ sS, int np,
                                           const uint32_t* __restrict__ queue, int count, int lane, const float* ctr, const float* hhalf) {
     using K = BwdCfg<D, FN, CB>;
@@ -334,25 +335,9 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
     } else {
     // CENTRED (fn 0, fast path): second moments about the tile centre from the staged sample products.  Accumulating
     // sum w x' x'^T in fp32 loses (|mu'| / |X|)^2 in relative precision (x' ~ mu' when the tile is much wider than the
-    // Gaussian's reach), so a batch takes this form only if the tile's half diagonal lies within 1.5x the tau ellipsoid
-    // of EVERY Gaussian of the batch (measured in the whitened metric); otherwise the per-pair products w X_i X_j.
-    bool centred_ok = false;
-    if constexpr (FN == 0 && FAST) {
-        bool ok = true;
-#pragma unroll
-        for (int g = 0; g < NG; g++) {
-            float th = 0.f;
-#pragma unroll
-            for (int i = 0; i < D; i++) {
-                float y = 0.f;
-#pragma unroll
-                for (int j = i; j < D; j++) y = fmaf(fabsf(geo[g][dgs_tri(D, i, j)]), hhalf[j], y);
-                th = fmaf(y, y, th);
-            }
-            ok = ok && (!valid[g] || th <= 2.25f * A.t_max);
-        }
-        centred_ok = __all_sync(0xffffffffu, ok);
-    }
+    // Gaussian's reach), so the LAUNCHER picks this form only when the fine tiles' half diagonal lies within 1.5x the
+    // narrow-axis tau reach of the smallest Gaussian (plan->min_reach); otherwise the per-pair products w X_i X_j.
+    constexpr bool centred_ok = CENTRED_K && FN == 0 && FAST;
     auto run_samples = [&](auto centred_tag) {
     constexpr bool CENTRED = decltype(centred_tag)::value != 0;
 #pragma unroll 2
@@ -433,12 +418,8 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
         }
     }
     };
-    if constexpr (FN == 0 && FAST) {
-        if (centred_ok) run_samples(DgsInt<1>{}); else run_samples(DgsInt<0>{});
-    } else {
-        run_samples(DgsInt<0>{});
-    }
-    if (centred_ok) {
+    run_samples(DgsInt<centred_ok ? 1 : 0>{});
+    if constexpr (centred_ok) {
         // sum w X X^T = S2' + mu' m1^T + m1 mu'^T - mu' mu'^T W,  S2' = sum w x' x'^T, mu' = mu - centre, m1 = sum w X, W = sum w
 #pragma unroll
         for (int g = 0; g < NG; g++) {
@@ -489,7 +470,7 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
     }
 }
 
-template <int D, int FN, int CB, bool VPOST>
+template <int D, int FN, int CB, bool VPOST, bool CENTRED_K>
 __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? BWD_TUNED : BWD_TUNED_3D) : BWD_MINB) dgs_backward_kernel(const BwdArgs A) {
     using K = BwdCfg<D, FN, CB>;
     constexpr int U = K::U, AFULL = K::AFULL, SW = K::SW, SW0 = K::SW0, SCAP = K::SCAP, NG = K::G;
@@ -630,7 +611,7 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     nq = remq;
                     __syncwarp();
                     if (nf >= 32 * NG) {
-                        bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, 32 * NG, lane, ctr, hhalf);
+                        bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, 32 * NG, lane, ctr, hhalf);
                         const int rem = nf - 32 * NG;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qF[32 * NG + lane];
@@ -640,7 +621,7 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         __syncwarp();
                     }
                     if (ng >= 32) {
-                        bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, 32, lane, ctr, hhalf);
+                        bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, 32, lane, ctr, hhalf);
                         const int rem = ng - 32;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qG[32 + lane];
@@ -655,10 +636,10 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     // leftovers (nf < 32 * NG, ng < 32) are processed here unconditionally: ids queued by an earlier
                     // drain must not depend on a later chunk of the list having a survivor for this tile
                     if (nf > 0) {
-                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST>(A, sS, np, qF, nf, lane, ctr, hhalf);
-                        else bwd_batch<D, FN, CB, 1, true, VPOST>(A, sS, np, qF, nf, lane, ctr, hhalf);
+                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, nf, lane, ctr, hhalf);
+                        else bwd_batch<D, FN, CB, 1, true, VPOST, CENTRED_K>(A, sS, np, qF, nf, lane, ctr, hhalf);
                     }
-                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST>(A, sS, np, qG, ng, lane, ctr, hhalf);
+                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, ng, lane, ctr, hhalf);
                     break;
                 }
             }
@@ -713,13 +694,19 @@ static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
     return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
 }
 
-template <int D, int FN, int CB, bool VPOST>
-static void bwd_launch_one(const BwdArgs& a, cudaStream_t st) {
-    auto kernel = dgs_backward_kernel<D, FN, CB, VPOST>;
+template <int D, int FN, int CB, bool VPOST, bool CENTRED_K>
+static void bwd_launch_one_c(const BwdArgs& a, cudaStream_t st) {
+    auto kernel = dgs_backward_kernel<D, FN, CB, VPOST, CENTRED_K>;
     DGS_PROF("backward_kernel", st);
     cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
     kernel<<<bwd_persistent_grid(kernel, a.n_tiles), BWD_THREADS, 0, st>>>(a);
     DGS_NOTE_LAUNCHES(1);
+}
+
+template <int D, int FN, int CB, bool VPOST>
+static void bwd_launch_one(const BwdArgs& a, cudaStream_t st) {
+    if (FN == 0 && a.centred) bwd_launch_one_c<D, FN, CB, VPOST, FN == 0>(a, st);
+    else bwd_launch_one_c<D, FN, CB, VPOST, false>(a, st);
 }
 
 template <int D, int FN>
@@ -775,6 +762,13 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.sched = (uint32_t*)(gbuf + plan->g_sched_off) + 1;     // the forward's counter is word 0
     a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
     a.t_max = dgs_tau_for(plan, dgs_mask_level(fn)) * 1.44269504088896340736f;
+    {
+        // nominal fine-tile half diagonal against the smallest narrow-axis reach at this function's tau
+        const float w = DGS_CELL / (float)(plan->F > 0 ? plan->F : 1);
+        const float half_diag = 0.5f * w * sqrtf((float)plan->D);
+        const float reach = plan->min_reach * sqrtf(dgs_tau_for(plan, dgs_mask_level(fn)) / (plan->tau + DGS_TAU_MAX_EXTRA));
+        a.centred = (plan->min_reach > 0.f && half_diag <= 1.5f * reach) ? 1 : 0;
+    }
     const int T = plan->D * (plan->D + 1) / 2;
     // the kernels accumulate: start from zero whatever the caller left in the buffers
     DGS_CUDA(cudaMemsetAsync(dmeans, 0, (size_t)plan->P * plan->D * 4, st));

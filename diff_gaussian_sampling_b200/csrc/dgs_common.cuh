@@ -72,7 +72,8 @@ struct DgsDevHeader {
     unsigned long long n_l1;
     double extent_sum;     // sum over Gaussians/axes of the cull half width (finite ones)
     unsigned long long extent_cnt;
-    uint32_t pad[8];
+    uint32_t min_reach_bits;   // ordered-int encoding of the smallest narrow-axis tau_max reach sqrt(2 tau_max / lambda_max(conic))
+    uint32_t pad[7];
 };
 #define DGS_HDR_EXACT_WRAP 1u
 #define DGS_HDR_OUTSIDE 2u

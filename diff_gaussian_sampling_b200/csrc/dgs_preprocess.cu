@@ -22,7 +22,7 @@
 __global__ void dgs_header_init_kernel(DgsDevHeader* h) {
     if (threadIdx.x == 0) {
         for (int d = 0; d < 3; d++) { h->lo_bits[d] = 0xffffffffu; h->hi_bits[d] = 0u; h->lo[d] = 0.f; h->hi[d] = 0.f; }
-        h->num_rendered = 0; h->flags = 0; h->n_l1 = 0; h->extent_sum = 0.0; h->extent_cnt = 0;
+        h->num_rendered = 0; h->flags = 0; h->n_l1 = 0; h->extent_sum = 0.0; h->extent_cnt = 0; h->min_reach_bits = 0xffffffffu;
     }
 }
 
@@ -108,6 +108,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
     double ext = 0.0;
     unsigned cnt = 0;
     uint32_t hflags = 0;
+    float reach_min = INFINITY;
     if (i < P) {
         float r_mu[3], r_R[3], r_rs2;
         float con[T];
@@ -168,6 +169,14 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
         }
         if (far) hflags |= DGS_HDR_EXACT_WRAP;
         bool small = true;
+        if (finite) {
+            // narrow-axis reach: 1 / lambda_max(conic) >= 1 / trace(conic) (a lower bound is what the consumer needs)
+            double tr = 0.0;
+            if (D == 1) tr = con[0];
+            else if (D == 2) tr = (double)con[0] + (double)con[2];
+            else tr = (double)con[0] + (double)con[3] + (double)con[5];
+            if (tr > 0.0) reach_min = fminf(reach_min, (float)sqrt(2.0 * (double)tau_max / tr));
+        }
         if (finite && !far) {
 #pragma unroll
             for (int d = 0; d < D; d++) {
@@ -208,6 +217,9 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_crec_kernel(const float* __re
         cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     }
     if (hflags) atomicOr(&s_flags, hflags);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) reach_min = fminf(reach_min, __shfl_xor_sync(0xffffffffu, reach_min, o));
+    if ((threadIdx.x & 31) == 0 && reach_min < INFINITY) atomicMin(&h->min_reach_bits, dgs_f2ord(reach_min));
     if ((threadIdx.x & 31) == 0) { s_ext[threadIdx.x >> 5] = ext; s_cnt[threadIdx.x >> 5] = cnt; }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -448,8 +460,9 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_sample_keys_kernel(const floa
         rank_of[i] = base + __popc(peers & ((1u << lane) - 1u));
     }
     if (FUSED) {
-        // bounding box of the tile's samples: warp-aggregated over the lanes of the same tile
-        if (valid) {
+        // bounding box of the tile's samples: warp-aggregated over the lanes of the same tile (only when the caller
+        // passes box arrays; measured slower than a separate pass, see dgs_api.cu)
+        if (valid && box_lo != nullptr) {
 #pragma unroll
             for (int d = 0; d < D; d++) {
                 const uint32_t o = dgs_f2ord(sv[d]);
@@ -683,7 +696,8 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
                                                              const float4* __restrict__ crec, const float* __restrict__ crecR,
                                                              float two_tau, int64_t P, DgsGrid G, int cpc,
                                                              int T1, int blocks,
-                                                             const float* __restrict__ coarse_aabb, uint32_t* __restrict__ tile_cnt,
+                                                             const float* __restrict__ coarse_aabb, const uint2* __restrict__ sample_ranges,
+                                                             uint32_t* __restrict__ tile_cnt,
                                                              unsigned long long* __restrict__ n1bits,
                                                              uint32_t* __restrict__ ids) {
     const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
@@ -750,6 +764,9 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         };
         dgs_for_each_cell<D>(p, r, G, [&](int cell) {
             if (cell >= G.n_ranges) return;
+            // a cell without samples (point shard of a multi-GPU job: most of them) has no tile to list the Gaussian in
+            const uint2 sr = __ldg(sample_ranges + cell);
+            if (sr.x == sr.y) return;
             const int64_t t0 = (int64_t)cell * cpc;
             if (always || cell >= blocks || T1 < 3) {
                 for (int t = 0; t < cpc; t++) test_tile(t0 + t);
@@ -793,8 +810,8 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
 }
 
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
-                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* tile_cnt, unsigned long long* n1bits,
-                  uint32_t* ids, cudaStream_t st) {
+                  const dgs_plan_t* plan, const float* coarse_aabb, const void* sample_ranges, uint32_t* tile_cnt,
+                  unsigned long long* n1bits, uint32_t* ids, cudaStream_t st) {
     DGS_PROF(emit ? "l1_emit" : "l1_count", st);
     const int64_t P = plan->P;
     if (P <= 0) return 0;
@@ -805,8 +822,8 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const float
     const int cpc = plan->coarse_per_cell;
     const float two_tau = 2.0f * (plan->tau + DGS_TAU_MAX_EXTRA);
 #define L1_LAUNCH(DD)                                                                                                         \
-    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, tile_cnt, n1bits, ids); \
-    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, tile_cnt, n1bits, ids);
+    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, (const uint2*)sample_ranges, tile_cnt, n1bits, ids); \
+    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, (const uint2*)sample_ranges, tile_cnt, n1bits, ids);
     if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
 #undef L1_LAUNCH
     DGS_NOTE_LAUNCHES(1);

@@ -24,8 +24,8 @@ int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const 
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
                          float* coarse_aabb, cudaStream_t st);
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
-                  const dgs_plan_t* plan, const float* coarse_aabb, uint32_t* tile_cnt, unsigned long long* n1bits,
-                  uint32_t* ids, cudaStream_t st);
+                  const dgs_plan_t* plan, const float* coarse_aabb, const void* sample_ranges, uint32_t* tile_cnt,
+                  unsigned long long* n1bits, uint32_t* ids, cudaStream_t st);
 int dgs_launch_l1_cursor_init(const uint32_t* start_tmp, int n, uint32_t* start_out, uint32_t* cursor, cudaStream_t st);
 int dgs_launch_l1_sort(const dgs_plan_t* plan, const uint32_t* l1_start, uint32_t* l1_ids, uint32_t* alt, cudaStream_t st);
 int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,

@@ -98,7 +98,9 @@ typedef struct dgs_plan {
     int32_t  samples_reused;       /* 1: the sample side of the buffers was carried over (dgs_plan_reuse_samples) */
     int32_t  reserved[2];
     uint64_t g_sched_off;          /* two uint32 work counters of the persistent accumulation kernels (forward, backward) */
-    uint64_t reserved2[3];
+    float    min_reach;            /* smallest narrow-axis reach sqrt(2 (tau+6) / trace(conic)) over the Gaussians (0: unknown) */
+    float    reserved3;
+    uint64_t reserved2[2];
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
