@@ -691,6 +691,11 @@ int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const ui
 // slop that covers the fp32 rounding of dgs_sample_cell / dgs_fine_coord) can reach the Gaussian's
 // tau box, or one of its period-2 images, are visited; the decision itself is always taken on the
 // bounding box of the samples actually in the tile.
+// Two phases per warp.  (A) every lane walks the candidate tiles of its own Gaussian — integer work only — and parks the
+// first L1_CAPL of them in shared memory; (B) the warp then works through ALL parked (Gaussian, tile) items 32 at a time:
+// box load + cull test + counter update (count pass), cursor grab + id store (emit pass) at full lane width.  Round 1 ran the
+// test inside the per-Gaussian loops at 10-13 active lanes per warp (ncu, profiles/r02_ncu_preprocess_blocks.txt).
+#define L1_CAPL 16
 template <int D, bool EMIT>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __restrict__ means, const float* __restrict__ radii,
                                                              const float4* __restrict__ crec, const float* __restrict__ crecR,
@@ -700,11 +705,30 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
                                                              uint32_t* __restrict__ tile_cnt,
                                                              unsigned long long* __restrict__ n1bits,
                                                              uint32_t* __restrict__ ids) {
+    __shared__ uint32_t s_q[DGS_THREADS / 32][32][L1_CAPL];
+    __shared__ uint32_t s_pre[DGS_THREADS / 32][33];
+    __shared__ unsigned long long s_bits[DGS_THREADS / 32][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t i = (int64_t)blockIdx.x * DGS_THREADS + threadIdx.x;
-    if (i >= P) return;
-    const float r = radii[i];
-    unsigned long long bits_out = 0ull;
-    if (r > 0.f) {
+    const float r = i < P ? radii[i] : 0.f;
+    const bool live = i < P && r > 0.f;
+    unsigned long long bits = 0ull;
+    bool overflow = false;
+    uint32_t npush = 0;
+    if (!EMIT) s_bits[w][lane] = 0ull;
+    auto eval_tile = [&](const DgsCullRecView& rc, int64_t tile) {
+        bool pass = false;
+        const float4 a = __ldg((const float4*)(coarse_aabb + tile * 8));
+        const float4 b = __ldg((const float4*)(coarse_aabb + tile * 8) + 1);
+        const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
+        if (lo[0] <= hi[0]) {        // the tile has samples
+            DgsTileBox box;
+            box.set(lo, hi);
+            pass = dgs_cull_pass<D>(rc, box, 1.0f, 1.0f, two_tau);
+        }
+        return pass;
+    };
+    if (live) {
         float p[D];
 #pragma unroll
         for (int k = 0; k < D; k++) p[k] = means[i * D + k];
@@ -713,54 +737,31 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         const bool always = rec.rs2 < 0.f;
         // The count pass remembers the verdicts of the first 63 enumerated tiles in a bitmask, so that the
         // emit pass (same enumeration) does not reload the tile boxes and repeat the tests.
-        unsigned long long bits = EMIT ? n1bits[i] : 0ull;
+        if (EMIT) bits = n1bits[i];
         const bool use_bits = EMIT && !(bits >> 63);
         int ci = 0;
-        bool overflow = false;
-        uint32_t pend[8];
-        int npend = 0;
-        auto flush_pending = [&]() {
-            uint32_t pos[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++)
-                if (k < npend) pos[k] = atomicAdd(&tile_cnt[pend[k]], 1u);
-#pragma unroll
-            for (int k = 0; k < 8; k++)
-                if (k < npend) ids[pos[k]] = (uint32_t)i;
-            npend = 0;
-        };
-        auto test_tile = [&](int64_t tile) {
-            bool pass = false;
-            if (use_bits) {
-                pass = (bits >> ci) & 1ull;
-            } else {
-                const float4 a = __ldg((const float4*)(coarse_aabb + tile * 8));
-                const float4 b = __ldg((const float4*)(coarse_aabb + tile * 8) + 1);
-                const float lo[3] = {a.x, a.y, a.z}, hi[3] = {a.w, b.x, b.y};
-                if (lo[0] <= hi[0]) {        // the tile has samples
-                    DgsTileBox box;
-                    box.set(lo, hi);
-                    pass = dgs_cull_pass<D>(rec, box, 1.0f, 1.0f, two_tau);
-                }
-                if (!EMIT) {
+        auto visit = [&](int64_t tile) {
+            if (!EMIT) {
+                if (ci < L1_CAPL) {
+                    s_q[w][lane][npush++] = (uint32_t)tile;          // candidate ci == slot ci
+                } else {
+                    const bool pass = eval_tile(rec, tile);
                     if (ci < 63) bits |= (unsigned long long)pass << ci;
                     else overflow = true;
+                    if (pass) atomicAdd(&tile_cnt[tile], 1u);
+                }
+            } else {
+                const bool pass = use_bits ? (((bits >> ci) & 1ull) != 0ull) : eval_tile(rec, tile);
+                if (pass) {
+                    if (npush < L1_CAPL) {
+                        s_q[w][lane][npush++] = (uint32_t)tile;
+                    } else {
+                        const uint32_t pos = atomicAdd(&tile_cnt[tile], 1u);
+                        ids[pos] = (uint32_t)i;
+                    }
                 }
             }
             ci++;
-            if (pass) {
-                // count pass: one counter per coarse tile (fire-and-forget reduction); emit pass: the counters hold the
-                // running write cursors (initialised to the scanned starts), so the list of a tile is contiguous but in
-                // arrival order — dgs_l1_sort_kernel puts every list into ascending Gaussian id afterwards.  The emit
-                // pass first collects up to 8 tiles and then issues their atomics back to back: one round trip to L2 per
-                // batch instead of one per entry.
-                if (!EMIT) {
-                    atomicAdd(&tile_cnt[tile], 1u);
-                } else {
-                    pend[npend++] = (uint32_t)tile;
-                    if (npend == 8) flush_pending();
-                }
-            }
         };
         dgs_for_each_cell<D>(p, r, G, [&](int cell) {
             if (cell >= G.n_ranges) return;
@@ -769,7 +770,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
             if (sr.x == sr.y) return;
             const int64_t t0 = (int64_t)cell * cpc;
             if (always || cell >= blocks || T1 < 3) {
-                for (int t = 0; t < cpc; t++) test_tile(t0 + t);
+                for (int t = 0; t < cpc; t++) visit(t0 + t);
                 return;
             }
             int cc[3] = {0, 0, 0};
@@ -801,12 +802,42 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
             if (!any) return;
             for (int tz = tlo[2]; tz <= thi[2]; tz++)
                 for (int ty = tlo[1]; ty <= thi[1]; ty++)
-                    for (int tx = tlo[0]; tx <= thi[0]; tx++) test_tile(t0 + ((int64_t)tz * T1 + ty) * T1 + tx);
+                    for (int tx = tlo[0]; tx <= thi[0]; tx++) visit(t0 + ((int64_t)tz * T1 + ty) * T1 + tx);
         });
-        if (EMIT && npend > 0) flush_pending();
-        bits_out = overflow ? (1ull << 63) : bits;
     }
-    if (!EMIT) n1bits[i] = bits_out;
+    // ---- phase B: the parked items of the whole warp, 32 at a time ----
+    uint32_t inc = npush;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    s_pre[w][lane] = inc - npush;
+    if (lane == 31) s_pre[w][32] = inc;
+    __syncwarp();
+    const uint32_t total = s_pre[w][32];
+    const int64_t wbase = i - lane;
+    for (uint32_t j = lane; j < total; j += 32) {
+        int o = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1)
+            if (s_pre[w][o + step] <= j) o += step;
+        const uint32_t k = j - s_pre[w][o];
+        const int64_t tile = s_q[w][o][k];
+        const int64_t gid = wbase + o;
+        if (!EMIT) {
+            const DgsCullRecView rc = dgs_crec_load<D>(crec, gid);
+            if (eval_tile(rc, tile)) {
+                atomicAdd(&tile_cnt[tile], 1u);
+                atomicOr(&s_bits[w][o], 1ull << k);
+            }
+        } else {
+            const uint32_t pos = atomicAdd(&tile_cnt[tile], 1u);
+            ids[pos] = (uint32_t)gid;
+        }
+    }
+    __syncwarp();
+    if (!EMIT && i < P) n1bits[i] = live ? (overflow ? (1ull << 63) : (bits | s_bits[w][lane])) : 0ull;
 }
 
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
