@@ -405,6 +405,7 @@ def run_ours(args, rank, world, local_rank):
         flat_sh, out_sh = step(devt)
         flat_sh = flat_sh.clone()
         barrier()
+        saved_state = dict(state)     # the pair counts / roofline below describe THIS rank's shard, not the check's full set
         if rank == 0:
             try:
                 parts = [make_samples(args.workload, r, world, args.scaling) for r in range(world)]
@@ -427,6 +428,7 @@ def run_ours(args, rank, world, local_rank):
                 del full, flat_1, out_1
             except Exception as ex:  # noqa: BLE001
                 parity = {"status": "error", "error": repr(ex)[:300]}
+        state.clear(); state.update(saved_state)
         barrier()
     return dict(tot_ms=tot_ms, t_pre=t_pre, t_fwd=t_fwd, t_bwd=t_bwd, t_ar=t_ar, e2e=e2e, t_pre_reuse=t_pre_reuse, per_fn=per_fn,
                 clocks=clk, launches=launches, parity=parity,
