@@ -63,6 +63,9 @@ EXPORTS = {
     "dgs_plan_from_buffer": (ctypes.c_int, [c_vp, c_sz, c_u32, ctypes.POINTER(Plan), c_vp]),
     "dgs_sample_forward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
                                           c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dgs_static_scratch_max_gaussians": (c_sz, []),
+    "dgs_sample_forward_static_scratch": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
+                                                         c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_sample_backward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
                                            c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dgs_sample_jet_forward": (ctypes.c_int, [ctypes.POINTER(Plan), ctypes.c_int, c_vp, c_vp, c_vp, c_vp,

@@ -130,7 +130,9 @@ __device__ __forceinline__ uint32_t dgs_match_digit8(uint32_t d, bool valid) {
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                        const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
                        float* out, unsigned long long* pair_counter, cudaStream_t st,
-                       float* out_derivative = nullptr, float* out_hessian = nullptr);   // fn == DGS_FN_JET only
+                       float* out_derivative = nullptr, float* out_hessian = nullptr,    // fn == DGS_FN_JET only
+                       float* prec_scratch = nullptr, uint32_t* sched_scratch = nullptr); // both or neither: packed records and work
+                                                                                          // counter outside gbuf (dgs_sample_forward_static_scratch)
 int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                         const float* conics, const float* dout, uint8_t* gbuf, const uint8_t* sbuf,
                         const void* ranges, float* dmeans, float* dvalues, float* dconics, cudaStream_t st,

@@ -578,12 +578,13 @@ int dgs_launch_pack(const float* means, const float* conics, const float* values
 int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means, const float* values,
                        const float* conics, uint8_t* gbuf, const uint8_t* sbuf, const void* ranges,
                        float* out, unsigned long long* pair_counter, cudaStream_t st, float* out_derivative,
-                       float* out_hessian) {
+                       float* out_hessian, float* prec_scratch, uint32_t* sched_scratch) {
     (void)ranges;
     if (plan->N <= 0 || plan->n_coarse <= 0) return 0;
     FwdArgs a;
     a.values = values; a.conics = conics;
-    a.prec = (const float*)(gbuf + plan->g_prec_off);
+    float* prec = prec_scratch ? prec_scratch : (float*)(gbuf + plan->g_prec_off);
+    a.prec = prec;
     a.mask64 = plan->mask_bytes == 8 ? 1 : 0;
     a.mask = gbuf + plan->g_l1_mask_off + (size_t)dgs_mask_level(fn) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
@@ -595,7 +596,7 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
     a.out = out; a.out1 = out_derivative; a.out2 = out_hessian; a.pair_counter = pair_counter;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
-    a.sched = (uint32_t*)(gbuf + plan->g_sched_off);
+    a.sched = sched_scratch ? sched_scratch : (uint32_t*)(gbuf + plan->g_sched_off);
     a.prec_has_value = 0;
     a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
     if (pair_counter) {
@@ -605,7 +606,7 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
         DGS_LAUNCH_CHECK();
         return 0;
     }
-    int rc = dgs_launch_pack(means, conics, values, C, plan->P, plan->D, (float*)(gbuf + plan->g_prec_off), st);
+    int rc = dgs_launch_pack(means, conics, values, C, plan->P, plan->D, prec, st);
     if (rc) return rc;
     a.prec_has_value = C == 1 ? 1 : 0;
     if (plan->D == 1) fwd_launch_d<1>(a, fn, st);
@@ -615,6 +616,60 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------
+// dgs_sample_forward_static_scratch (include/dgs_b200.h): the forward pass for callers that cannot tolerate ANY
+// allocation around the call (CUDA graph capture, tight serving loops) and hand in a binning buffer they treat as
+// read-only.  No counterpart in the reference.  The two pieces of scratch
+// the forward pass writes — the per-call packed Gaussian records and the work counter of the persistent kernel, which
+// dgs_sample_forward keeps inside binning_dev — live in the file-scope device array below instead: a fixed
+// DGS_STATIC_SCRATCH_MAX_P * 48 B + 256 B = 3 MiB + 256 B per GPU that loads the library, held until the process exits.
+// The array name is only a host-side handle: the kernels are given the DEVICE address that cudaGetSymbolAddress returns
+// for the current device (looked up once per device).  All calls on a device share the array, it keeps the previous
+// call's contents (the records of the P Gaussians are rewritten in full and the counter is cleared by every call), and
+// two calls that overlap on the GPU (different streams) race on it.
+// ---------------------------------------------------------------------------------------
+#define DGS_STATIC_SCRATCH_BYTES ((size_t)DGS_STATIC_SCRATCH_MAX_P * 48 + 256)
+static __device__ __align__(256) unsigned char g_dgs_static_scratch[DGS_STATIC_SCRATCH_BYTES];
+
+static int dgs_static_scratch_ptr(unsigned char** out) {
+    static unsigned char* cached[64];
+    int dev = 0;
+    DGS_CUDA(cudaGetDevice(&dev));
+    DGS_REQUIRE(dev >= 0 && dev < 64, DGS_ERR_UNSUPPORTED, "device index out of range for the static scratch table");
+    if (cached[dev] == nullptr) {
+        void* p = nullptr;
+        DGS_CUDA(cudaGetSymbolAddress(&p, g_dgs_static_scratch));     // the address on the CURRENT device
+        DGS_REQUIRE(p != nullptr, DGS_ERR_UNSUPPORTED, "cudaGetSymbolAddress returned a null scratch address");
+        cached[dev] = (unsigned char*)p;
+    }
+    *out = cached[dev];
+    return 0;
+}
+
+extern "C" __attribute__((visibility("default"))) size_t dgs_static_scratch_max_gaussians(void) { return (size_t)DGS_STATIC_SCRATCH_MAX_P; }
+
+extern "C" __attribute__((visibility("default"))) int dgs_sample_forward_static_scratch(
+    const dgs_plan_t* plan, int fn, int C, const float* means_dev, const float* values_dev, const float* conics_dev,
+    const float* samples_dev, const void* binning_dev, const void* sample_binning_dev, const void* ranges_dev,
+    const void* sample_ranges_dev, float* out_dev, void* stream) {
+    (void)samples_dev; (void)sample_ranges_dev;
+    DGS_REQUIRE(plan && plan->magic == DGS_PLAN_MAGIC && plan->abi == DGS_ABI_VERSION, DGS_ERR_BAD_PLAN, "bad plan (magic/abi)");
+    DGS_REQUIRE(plan->D >= 1 && plan->D <= 3 && plan->n_coarse > 0 && plan->n_fine > 0, DGS_ERR_BAD_PLAN, "bad plan (fields)");
+    DGS_REQUIRE(fn >= 0 && fn <= 3 && C >= 1, DGS_ERR_BAD_ARG, "fn must be 0..3 and C >= 1");
+    if (plan->P > (int64_t)DGS_STATIC_SCRATCH_MAX_P) {
+        dgs_set_error("dgs_sample_forward_static_scratch: P = %lld Gaussians exceed the static scratch (at most %d); use dgs_sample_forward",
+                      (long long)plan->P, (int)DGS_STATIC_SCRATCH_MAX_P);
+        return DGS_ERR_BUFFER_TOO_SMALL;
+    }
+    unsigned char* scratch = nullptr;
+    int rc = dgs_static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    // layout: [work counter, 256 B][packed records, P * DGS_PREC_W(D) floats]
+    return dgs_launch_forward(plan, fn, C, means_dev, values_dev, conics_dev, (uint8_t*)const_cast<void*>(binning_dev),
+                              (const uint8_t*)sample_binning_dev, ranges_dev, out_dev, nullptr, (cudaStream_t)stream, nullptr,
+                              nullptr, (float*)(scratch + 256), (uint32_t*)scratch);
+}
 
 // ---------------------------------------------------------------------------------------
 // Diagnostic (roofline accounting): of the pairs the accumulation kernels evaluate for function level `fn`, how many

@@ -209,6 +209,26 @@ int dgs_sample_forward(const dgs_plan_t* plan, int fn, int C,
                        float* out_dev, void* stream);
 
 /*
+ * dgs_sample_forward without any allocation and without writing into binning_dev.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc around the call (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it) or that share one read-only binning buffer.  Same arguments,
+ * results and error codes as dgs_sample_forward; the per-call scratch (packed Gaussian records + the work counter of
+ * the persistent kernel) lives in a file-scope `static __device__` array of the library instead of binning_dev:
+ * DGS_STATIC_SCRATCH_MAX_P * 48 B + 256 B = 3 MiB + 256 B on every GPU that loads the library, until the process exits.
+ * Limit: plan->P <= DGS_STATIC_SCRATCH_MAX_P (dgs_static_scratch_max_gaussians()), otherwise
+ * DGS_ERR_BUFFER_TOO_SMALL with a message in dgs_last_error().  Calls no cudaMalloc / cudaFree.  All calls on one
+ * device share the array: calls that overlap on the GPU (different streams) RACE — keep them stream-ordered.
+ */
+#define DGS_STATIC_SCRATCH_MAX_P 65536
+size_t dgs_static_scratch_max_gaussians(void);
+int dgs_sample_forward_static_scratch(const dgs_plan_t* plan, int fn, int C,
+                                      const float* means_dev, const float* values_dev, const float* conics_dev,
+                                      const float* samples_dev,
+                                      const void* binning_dev, const void* sample_binning_dev,
+                                      const void* ranges_dev, const void* sample_ranges_dev,
+                                      float* out_dev, void* stream);
+
+/*
  * Backward of the above (reference: SampleGaussians*BackwardCUDA, sample_points.cu:145-196,
  * 299-372; kernels backward.cu:26-416).  dmeans (P,D), dvalues (P,C), dconics (P,D(D+1)/2)
  * are overwritten (the reference allocates them zero-filled, sample_points.cu:165-167, and
