@@ -219,6 +219,7 @@ static void gauss_layout(dgs_plan_t* pl) {
     pl->g_crec_off = o; o = dgs_a128(o + p * dgs_crec_bytes(pl->D));
     pl->g_l1_start_off = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     pl->g_l1_ids_off = o; o = dgs_a128(o + (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * 4);
+    pl->g_cflag_off = o; o = dgs_a128(o + ((size_t)pl->n_coarse + 1) * 4);
     pl->g_prec_off = o; o = dgs_a128(o + p * (size_t)(pl->D == 3 ? 12 : 8) * 4);
     pl->mask_bytes = pl->fine_per_coarse > 32 ? 8 : 4;
     pl->g_l1_mask_off = o; o = dgs_a128(o + 4 * (size_t)(pl->n_l1 > 0 ? pl->n_l1 : 1) * (size_t)pl->mask_bytes);
@@ -599,7 +600,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
         rc = dgs_launch_l1_sort(plan, l1_start, l1_ids, (uint32_t*)(tmp + tl.l1_alt), st);
         if (rc) return rc;
         rc = dgs_launch_l1_masks(plan, l1_start, l1_ids, crec, (const float*)(sb + plan->s_fine_aabb_off), coarse_aabb,
-                                 gb + plan->g_l1_mask_off, st);
+                                 gb + plan->g_l1_mask_off, (uint32_t*)(gb + plan->g_cflag_off), st);
         if (rc) return rc;
     }
     static_assert(sizeof(dgs_plan_t) % 4 == 0 && sizeof(dgs_plan_t) <= 2048, "plan travels as a kernel argument");

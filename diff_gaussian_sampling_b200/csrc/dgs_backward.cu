@@ -61,6 +61,7 @@ struct BwdArgs {
     const float* prec;
     const void* mask; int mask64;                 // survivor bitmasks of this function level
     const uint32_t* l1_start; const uint32_t* l1_ids;
+    const uint32_t* cflag;                        // per coarse tile: 1 = the tile-centred pair form is numerically safe (dgs_l1_mask_kernel)
     const uint32_t* fine_start; const uint32_t* fine_ids; const float* fine_xyz;
     const float* fine_aabb; const float* coarse_aabb;
     float* dmeans; float* dvalues; float* dconics;
@@ -68,6 +69,7 @@ struct BwdArgs {
     int64_t N;
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
+    uint32_t grab;                                // fine tiles per grab of the work counter (BWD_GRAB, or 1 when a rank has few tiles per warp: shorter tail)
     float t_max;                                  // tau of this function level x log2(e): |U X|^2 beyond it is culled
     int centred;                                  // fn 0: second moments about the tile centre are numerically safe (launcher)
 };
@@ -81,9 +83,17 @@ struct BwdCfg {
     // accumulated about that centre with ONE FFMA per component and pair, the operand coming straight from shared memory)
     static constexpr int PO = D + U * CB;
     static constexpr int SW0 = PO + (FN == 0 ? T : 0);
+    // fn 0, one channel: tiles in the tile-centred form stage TWO samples per record, component-interleaved
+    //   [x'_d (a, b)]_D | dO (a, b) | [x'_i x'_j (a, b)]_T | [x_d exact (a, b)]_D        (PRW floats per sample pair)
+    // so that every packed operand of the pair loop is an aligned register pair straight out of an LDS.128; the exact
+    // coordinates ride along for the literal general path ((x - c) + c is not x)
+    static constexpr bool CEN_OK = (FN == 0 && CB == 1);
+    static constexpr int PR_X = 2 * (D + 1 + T);                       // float offset of the exact coordinates
+    static constexpr int PRW = (2 * (D + 1 + T + D) + 3) / 4 * 4;
     static constexpr int SW = (SW0 + 3) / 4 * 4;
     static constexpr int SAMP_FLOATS = 224 * SW < 2048 ? 224 * SW : 2048;
     static constexpr int SCAP = SAMP_FLOATS / SW;           // samples per pass
+    static constexpr int SCAP_P = 2 * (SAMP_FLOATS / PRW) < SCAP ? 2 * (SAMP_FLOATS / PRW) : SCAP;   // ... of a centred tile
     static constexpr int G = FN == 0 ? 2 : (D <= 2 ? BWD_NG_HI : 1);   // Gaussians per lane on the fast path
     static constexpr int WARP_WORDS = SAMP_FLOATS + BWD_QF + BWD_QG + BWD_QRAW;
 };
@@ -251,9 +261,111 @@ __device__ __forceinline__ void bwd_pair(const float* X, const float* a, float G
     }
 }
 
+// One batch in the tile-centred form (fn 0, one channel, whitened fast path; dgs_field.cuh).  Every pair is
+//   t = |U x' + nb|^2,  w = 2^-t dO,  W += w,  S1 += w x',  S2 += w x' x'^T
+// with all operands but the Gaussian's own U / nb taken from the staged sample-pair record.  TWO SAMPLES ride in the
+// halves of every packed FP32 operand (the Gaussian's constants are broadcast operands), so no register pair has to be
+// assembled inside the loop; the two halves of each accumulator are added once per batch.  The moments about the
+// Gaussian's mean follow once per batch:  sum w X = m W - S1,  sum w X X^T = S2 - m S1^T - S1 m^T + m m^T W,
+// m = mu - centre.  npair = ceil(np / 2): an odd last sample is staged with a zero partner (dO = 0).
+template <int D, int NG>
+__device__ __forceinline__ void bwd_batch_centred(const BwdArgs& A, const float* __restrict__ sS, int npair,
+                                                  const uint32_t* __restrict__ queue, int count, int lane, const float* ctr) {
+    using K = BwdCfg<D, 0, 1>;
+    constexpr int T = K::T, PRW = K::PRW;
+    constexpr int NL = 2 * (D + 1 + T);            // floats of a pair record the fast path reads
+    constexpr int PW = DGS_PREC_W(D);
+    uint32_t id[NG];
+    bool valid[NG];
+    float Ug[NG][T], nb[NG][D];
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+        const int qi = lane + 32 * g;
+        valid[g] = qi < count;
+        id[g] = queue[valid[g] ? qi : 0] & ~BWD_EXACT_BIT;
+        const float4* p4 = (const float4*)(A.prec + (int64_t)id[g] * PW);
+        float pr[PW];
+#pragma unroll
+        for (int q = 0; q < PW / 4; q++) {
+            const float4 v = __ldg(p4 + q);
+            pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
+        }
+#pragma unroll
+        for (int k = 0; k < T; k++) Ug[g][k] = pr[D + k];
+        dgs_centred_nb<D>(pr, pr + D, ctr, nb[g]);
+    }
+    float2 W2[NG], S12[NG][D], S22[NG][T];
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+        W2[g] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int d = 0; d < D; d++) S12[g][d] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < T; k++) S22[g][k] = make_float2(0.f, 0.f);
+    }
+    for (int j = 0; j < npair; j++) {
+        float f[(NL + 3) / 4 * 4];
+#pragma unroll
+        for (int q = 0; q < (NL + 3) / 4; q++) {
+            const float4 v = *(const float4*)(sS + j * PRW + q * 4);
+            f[q * 4] = v.x; f[q * 4 + 1] = v.y; f[q * 4 + 2] = v.z; f[q * 4 + 3] = v.w;
+        }
+        float2 xp[D], pp[T];
+#pragma unroll
+        for (int d = 0; d < D; d++) xp[d] = make_float2(f[2 * d], f[2 * d + 1]);
+        const float2 dO2 = make_float2(f[2 * D], f[2 * D + 1]);
+#pragma unroll
+        for (int k = 0; k < T; k++) pp[k] = make_float2(f[2 * (D + 1 + k)], f[2 * (D + 1 + k) + 1]);
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            float2 U2[T], nb2[D];
+#pragma unroll
+            for (int k = 0; k < T; k++) U2[k] = dgs_bc2(Ug[g][k]);
+#pragma unroll
+            for (int d = 0; d < D; d++) nb2[d] = dgs_bc2(nb[g][d]);
+            const float2 t2 = dgs_white_t2_centred<D>(xp, U2, nb2);
+            const float2 w2 = __fmul2_rn(make_float2(dgs_ex2(-t2.x), dgs_ex2(-t2.y)), dO2);
+            W2[g] = __fadd2_rn(W2[g], w2);
+#pragma unroll
+            for (int d = 0; d < D; d++) S12[g][d] = __ffma2_rn(w2, xp[d], S12[g][d]);
+#pragma unroll
+            for (int k = 0; k < T; k++) S22[g][k] = __ffma2_rn(w2, pp[k], S22[g][k]);
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+        if (valid[g]) {
+            const float W = W2[g].x + W2[g].y;
+            float S1[D], S2[T], M1[D], m[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) S1[d] = S12[g][d].x + S12[g][d].y;
+#pragma unroll
+            for (int k = 0; k < T; k++) S2[k] = S22[g][k].x + S22[g][k].y;
+#pragma unroll
+            for (int d = 0; d < D; d++) m[d] = __ldg(A.prec + (int64_t)id[g] * PW + d) - ctr[d];
+#pragma unroll
+            for (int d = 0; d < D; d++) M1[d] = fmaf(m[d], W, -S1[d]);
+            atomicAdd(A.dvalues + (int64_t)id[g] * A.C + A.ch0, W);
+#pragma unroll
+            for (int d = 0; d < D; d++) atomicAdd(A.dmeans + (int64_t)id[g] * D + d, M1[d]);
+#pragma unroll
+            for (int i = 0; i < D; i++)
+#pragma unroll
+                for (int jx = i; jx < D; jx++) {
+                    // S2 - m_i S1_j - m_j S1_i + m_i m_j W  ==  S2 - m_i S1_j + m_j M1_i
+                    float c2 = S2[dgs_tri(D, i, jx)];
+                    c2 = fmaf(-m[i], S1[jx], c2);
+                    c2 = fmaf(m[jx], M1[i], c2);
+                    atomicAdd(A.dconics + (int64_t)id[g] * T + dgs_tri(D, i, jx), c2);
+                }
+        }
+    }
+}
+
 // One batch: every lane owns NG Gaussians (queue entries lane, lane+32, ...) and walks the np
 // staged samples.  FAST: whitened geometry without wrap; otherwise the literal reference pair.
-template <int D, int FN, int CB, int NG, bool FAST, bool VPOST, bool CENTRED_K>
+// PAIRED: the tile is staged in the sample-pair layout of the centred form (BwdCfg); only the literal general path runs here then.
+template <int D, int FN, int CB, int NG, bool FAST, bool VPOST, bool CENTRED_K, bool PAIRED = false>
 __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restrict__ sS, int np,
                                           const uint32_t* __restrict__ queue, int count, int lane, const float* ctr, const float* hhalf) {
     using K = BwdCfg<D, FN, CB>;
@@ -343,12 +455,20 @@ DGS_UNROLL(BWD_PACKED_UNROLL)
 #pragma unroll 2
     for (int s = 0; s < np; s++) {
         float sr[SW];
+        if constexpr (PAIRED) {
+            // exact coordinates and dO of sample s out of its pair record (fn 0, one channel; rare path)
+            const float* rp = sS + (s >> 1) * K::PRW + (s & 1);
+#pragma unroll
+            for (int d = 0; d < D; d++) sr[d] = rp[K::PR_X + 2 * d];
+            sr[D] = rp[2 * D];
+        } else {
 #pragma unroll
         for (int q = 0; q < SW / 4; q++) {
             if (q * 4 < SW0) {
                 const float4 v = *(const float4*)(sS + s * SW + q * 4);
                 sr[q * 4] = v.x; sr[q * 4 + 1] = v.y; sr[q * 4 + 2] = v.z; sr[q * 4 + 3] = v.w;
             }
+        }
         }
 #pragma unroll
         for (int g = 0; g < NG; g++) {
@@ -485,12 +605,12 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     uint32_t* qR = qG + BWD_QG;
     // persistent warps pulling fine tiles from a global counter (see dgs_forward.cu)
     uint32_t nx = 0;
-    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)BWD_GRAB);
+    if (lane == 0) nx = atomicAdd(A.sched, A.grab);
     for (;;) {
     const uint32_t grab = __shfl_sync(0xffffffffu, nx, 0);
     if (grab >= A.n_tiles) break;
-    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)BWD_GRAB);
-    for (uint32_t gj = 0; gj < BWD_GRAB; gj++) {
+    if (lane == 0) nx = atomicAdd(A.sched, A.grab);
+    for (uint32_t gj = 0; gj < A.grab; gj++) {
         const uint32_t tile32 = grab + gj;
         if (tile32 >= A.n_tiles) break;
         const int64_t tile = tile32;
@@ -509,15 +629,47 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
         float ctr[3], hhalf[3];
 #pragma unroll
         for (int d = 0; d < 3; d++) { ctr[d] = 0.5f * (lo[d] + hi[d]); hhalf[d] = 0.5f * (hi[d] - lo[d]); }
+        // tile-centred pair form (warp-uniform): fn 0, one channel, and only where the preprocess found it safe
+        bool cen = false;
+        if constexpr (K::CEN_OK && VPOST) cen = A.cflag[coarse] != 0u;
 
         const uint32_t n = s1 - s0;
-        const uint32_t n_pass = (n + SCAP - 1) / SCAP;
+        const uint32_t cap = cen ? (uint32_t)K::SCAP_P : (uint32_t)SCAP;
+        const uint32_t n_pass = (n + cap - 1) / cap;
         const uint32_t per = (n + n_pass - 1) / n_pass;
         for (uint32_t pb = s0; pb < s1; pb += per) {
             const int np = (int)(min(s1, pb + per) - pb);
             __syncwarp();
             // ---- stage the samples of this pass: x and the symmetrised dL/dout ----
-            for (int sl = lane; sl < np; sl += 32) {
+            bool staged = false;
+            if constexpr (K::CEN_OK && VPOST) {
+                if (cen) {
+                    // sample-pair layout of the centred form; an odd last sample gets a zero partner at the tile centre
+                    const int np2 = (np + 1) & ~1;
+                    for (int sl = lane; sl < np2; sl += 32) {
+                        float* r = sS + (sl >> 1) * K::PRW + (sl & 1);
+                        float xe[D], xc[D], dO = 0.f;
+                        if (sl < np) {
+                            const uint32_t jj = pb + sl;
+#pragma unroll
+                            for (int d = 0; d < D; d++) { xe[d] = A.fine_xyz[(int64_t)d * A.N + jj]; xc[d] = xe[d] - ctr[d]; }
+                            dO = A.dout[(int64_t)A.fine_ids[jj] * A.C + A.ch0];
+                        } else {
+#pragma unroll
+                            for (int d = 0; d < D; d++) { xe[d] = ctr[d]; xc[d] = 0.f; }
+                        }
+#pragma unroll
+                        for (int d = 0; d < D; d++) { r[2 * d] = xc[d]; r[K::PR_X + 2 * d] = xe[d]; }
+                        r[2 * D] = dO;
+#pragma unroll
+                        for (int i = 0; i < D; i++)
+#pragma unroll
+                            for (int j = i; j < D; j++) r[2 * (D + 1 + dgs_tri(D, i, j))] = xc[i] * xc[j];
+                    }
+                    staged = true;
+                }
+            }
+            for (int sl = lane; sl < np && !staged; sl += 32) {
                 const uint32_t jj = pb + sl;
                 const uint32_t sid = A.fine_ids[jj];
                 float* r = sS + sl * SW;
@@ -611,7 +763,12 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                     nq = remq;
                     __syncwarp();
                     if (nf >= 32 * NG) {
-                        bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, 32 * NG, lane, ctr, hhalf);
+                        if constexpr (K::CEN_OK && VPOST) {
+                            if (cen) bwd_batch_centred<D, NG>(A, sS, (np + 1) >> 1, qF, 32 * NG, lane, ctr);
+                            else bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, 32 * NG, lane, ctr, hhalf);
+                        } else {
+                            bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, 32 * NG, lane, ctr, hhalf);
+                        }
                         const int rem = nf - 32 * NG;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qF[32 * NG + lane];
@@ -621,7 +778,12 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         __syncwarp();
                     }
                     if (ng >= 32) {
-                        bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, 32, lane, ctr, hhalf);
+                        if constexpr (K::CEN_OK && VPOST) {
+                            if (cen) bwd_batch<D, FN, CB, 1, false, VPOST, false, true>(A, sS, np, qG, 32, lane, ctr, hhalf);
+                            else bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, 32, lane, ctr, hhalf);
+                        } else {
+                            bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, 32, lane, ctr, hhalf);
+                        }
                         const int rem = ng - 32;          // < 32
                         uint32_t kp = 0;
                         if (lane < rem) kp = qG[32 + lane];
@@ -635,11 +797,24 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                 if (end) {
                     // leftovers (nf < 32 * NG, ng < 32) are processed here unconditionally: ids queued by an earlier
                     // drain must not depend on a later chunk of the list having a survivor for this tile
-                    if (nf > 0) {
-                        if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, nf, lane, ctr, hhalf);
-                        else bwd_batch<D, FN, CB, 1, true, VPOST, CENTRED_K>(A, sS, np, qF, nf, lane, ctr, hhalf);
+                    bool done = false;
+                    if constexpr (K::CEN_OK && VPOST) {
+                        if (cen) {
+                            if (nf > 0) {
+                                if (NG > 1 && nf > 32) bwd_batch_centred<D, NG>(A, sS, (np + 1) >> 1, qF, nf, lane, ctr);
+                                else bwd_batch_centred<D, 1>(A, sS, (np + 1) >> 1, qF, nf, lane, ctr);
+                            }
+                            if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST, false, true>(A, sS, np, qG, ng, lane, ctr, hhalf);
+                            done = true;
+                        }
                     }
-                    if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, ng, lane, ctr, hhalf);
+                    if (!done) {
+                        if (nf > 0) {
+                            if (NG > 1 && nf > 32) bwd_batch<D, FN, CB, NG, true, VPOST, CENTRED_K>(A, sS, np, qF, nf, lane, ctr, hhalf);
+                            else bwd_batch<D, FN, CB, 1, true, VPOST, CENTRED_K>(A, sS, np, qF, nf, lane, ctr, hhalf);
+                        }
+                        if (ng > 0) bwd_batch<D, FN, CB, 1, false, VPOST, CENTRED_K>(A, sS, np, qG, ng, lane, ctr, hhalf);
+                    }
                     break;
                 }
             }
@@ -679,7 +854,7 @@ int dgs_mask_level(int fn);
 int dgs_launch_pack(const float* means, const float* conics, const float* values, int C, int64_t P, int D, float* prec, cudaStream_t st);
 
 template <typename KernelT>
-static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
+static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles, uint32_t* grab) {
     static int cached[64];
     int dev = 0;
     cudaGetDevice(&dev);
@@ -690,7 +865,9 @@ static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, BWD_THREADS, 0) != cudaSuccess || occ < 1) { occ = 1; (void)cudaGetLastError(); }
         cached[dev] = sms * occ;
     }
-    const int64_t need = ((int64_t)n_tiles + BWD_WARPS * BWD_GRAB - 1) / (BWD_WARPS * BWD_GRAB);
+    // few tiles per resident warp (a point shard of a multi-GPU job): grab one tile at a time, the tail is one tile long
+    *grab = ((int64_t)n_tiles >= (int64_t)16 * cached[dev] * BWD_WARPS) ? (uint32_t)BWD_GRAB : 1u;
+    const int64_t need = ((int64_t)n_tiles + BWD_WARPS * *grab - 1) / (BWD_WARPS * *grab);
     return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
 }
 
@@ -699,7 +876,9 @@ static void bwd_launch_one_c(const BwdArgs& a, cudaStream_t st) {
     auto kernel = dgs_backward_kernel<D, FN, CB, VPOST, CENTRED_K>;
     DGS_PROF("backward_kernel", st);
     cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
-    kernel<<<bwd_persistent_grid(kernel, a.n_tiles), BWD_THREADS, 0, st>>>(a);
+    BwdArgs b = a;
+    const int grid = bwd_persistent_grid(kernel, a.n_tiles, &b.grab);
+    kernel<<<grid, BWD_THREADS, 0, st>>>(b);
     DGS_NOTE_LAUNCHES(1);
 }
 
@@ -752,6 +931,7 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.mask = gbuf + plan->g_l1_mask_off + (size_t)dgs_mask_level(fn) * (size_t)plan->n_l1 * (size_t)plan->mask_bytes;
     a.l1_start = (const uint32_t*)(gbuf + plan->g_l1_start_off);
     a.l1_ids = (const uint32_t*)(gbuf + plan->g_l1_ids_off);
+    a.cflag = (const uint32_t*)(gbuf + plan->g_cflag_off);
     a.fine_start = (const uint32_t*)(sbuf + plan->s_fine_start_off);
     a.fine_ids = (const uint32_t*)(sbuf + plan->s_fine_ids_off);
     a.fine_xyz = (const float*)(sbuf + plan->s_fine_xyz_off);

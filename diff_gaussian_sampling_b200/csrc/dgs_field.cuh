@@ -218,6 +218,75 @@ __device__ __forceinline__ float2 dgs_white_t2(const float2* X, const float2* U)
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Tile-centred whitened form (backward of `gaussian`, fast path).  With c the centre of the box of the tile's samples,
+// x' = x - c (taken once per staged sample) and nb = -U (mu - c) (taken once per Gaussian and tile):
+//     U (mu - x) = -(U x' + nb),      |U X|^2 = |U x' + nb|^2,
+// i.e. the D subtractions per pair disappear, and the moments are accumulated about the tile centre
+// (W = sum w, S1 = sum w x', S2 = sum w x' x'^T: every operand but the Gaussian's own U / nb is a staged sample value)
+// and shifted to the Gaussian's mean once per batch: 12 instead of 14 FMA-pipe operations per 2D pair, 20 instead of
+// 23 in 3D.  The price is cancellation between U x' and nb: the rounding error of |U X| grows like
+// 2^-24 (|U x'| + |nb|), so the form is used only on the coarse tiles whose list the preprocess found safe (every listed
+// Gaussian has h^T (log2(e)/2 |C|) h <= DGS_CENTRED_U2MAX over each fine tile's sample box, dgs_l1_mask_kernel), which
+// bounds |nb| <= sqrt(U2MAX) + sqrt(tau_max log2 e) for every surviving pair.
+//
+// TWO SAMPLES ride in the halves of the packed FP32 operands and the Gaussian's constants are broadcast operands (pairing
+// the lane's two Gaussians instead made ptxas re-assemble the loop-invariant pairs inside the loop: 7-13 IMAD.MOV per 4
+// pairs, on the FMA pipe the loop is bound by).
+// ---------------------------------------------------------------------------------------
+#define DGS_CENTRED_U2MAX 12.25f
+// |U x' + nb|^2 for two samples (the halves of x) of one Gaussian (U, nb broadcast)
+template <int D>
+__device__ __forceinline__ float2 dgs_white_t2_centred(const float2* x, const float2* U, const float2* nb) {
+    if (D == 1) {
+        const float2 y = __ffma2_rn(U[0], x[0], nb[0]);
+        return __fmul2_rn(y, y);
+    } else if (D == 2) {
+        const float2 y0 = __ffma2_rn(U[0], x[0], __ffma2_rn(U[1], x[1], nb[0]));
+        const float2 y1 = __ffma2_rn(U[2], x[1], nb[1]);
+        return __ffma2_rn(y0, y0, __fmul2_rn(y1, y1));
+    } else {
+        const float2 y0 = __ffma2_rn(U[0], x[0], __ffma2_rn(U[1], x[1], __ffma2_rn(U[2], x[2], nb[0])));
+        const float2 y1 = __ffma2_rn(U[3], x[1], __ffma2_rn(U[4], x[2], nb[1]));
+        const float2 y2 = __ffma2_rn(U[5], x[2], nb[2]);
+        return __ffma2_rn(y0, y0, __ffma2_rn(y1, y1, __fmul2_rn(y2, y2)));
+    }
+}
+// scalar twin (same operations in the same order: bit-identical to either half of the packed form)
+template <int D>
+__device__ __forceinline__ float dgs_white_t_centred(const float* x, const float* U, const float* nb) {
+    if (D == 1) {
+        const float y = fmaf(U[0], x[0], nb[0]);
+        return y * y;
+    } else if (D == 2) {
+        const float y0 = fmaf(U[0], x[0], fmaf(U[1], x[1], nb[0]));
+        const float y1 = fmaf(U[2], x[1], nb[1]);
+        return fmaf(y0, y0, y1 * y1);
+    } else {
+        const float y0 = fmaf(U[0], x[0], fmaf(U[1], x[1], fmaf(U[2], x[2], nb[0])));
+        const float y1 = fmaf(U[3], x[1], fmaf(U[4], x[2], nb[1]));
+        const float y2 = fmaf(U[5], x[2], nb[2]);
+        return fmaf(y0, y0, fmaf(y1, y1, y2 * y2));
+    }
+}
+// nb = -U (mu - c) from the packed record's mu and U
+template <int D>
+__device__ __forceinline__ void dgs_centred_nb(const float* mu, const float* U, const float* ctr, float* nb) {
+    float m[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) m[d] = mu[d] - ctr[d];
+    if (D == 1) {
+        nb[0] = -(U[0] * m[0]);
+    } else if (D == 2) {
+        nb[0] = -fmaf(U[0], m[0], U[1] * m[1]);
+        nb[1] = -(U[2] * m[1]);
+    } else {
+        nb[0] = -fmaf(U[0], m[0], fmaf(U[1], m[1], U[2] * m[2]));
+        nb[1] = -fmaf(U[3], m[1], U[4] * m[2]);
+        nb[2] = -(U[5] * m[2]);
+    }
+}
+
 // a = C X from the packed conic
 template <int D>
 __device__ __forceinline__ void dgs_conic_times(const float* con, const float* X, float* a) {

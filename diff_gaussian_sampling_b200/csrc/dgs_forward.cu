@@ -57,6 +57,7 @@ struct FwdArgs {
     int64_t N;
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
+    uint32_t grab;                                // fine tiles per grab of the work counter (FWD_GRAB, or 1 when a rank has few tiles per warp: shorter tail)
     int prec_has_value;                           // C == 1: the packed records carry values[:, 0] (dgs_pack.cu)
 };
 
@@ -242,12 +243,12 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     // the warps of an SM mostly share coarse lists in L1/L2; no static assignment means no tail (round 1: one CTA per
     // coarse tile, 12 % of the SM cycles idle at the end of the forward kernel).
     uint32_t nx = 0;                                   // lane 0: the grab in flight
-    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)FWD_GRAB);
+    if (lane == 0) nx = atomicAdd(A.sched, A.grab);
     for (;;) {
     const uint32_t grab = __shfl_sync(0xffffffffu, nx, 0);
     if (grab >= A.n_tiles) break;
-    if (lane == 0) nx = atomicAdd(A.sched, (uint32_t)FWD_GRAB);
-    for (uint32_t gj = 0; gj < FWD_GRAB; gj++) {
+    if (lane == 0) nx = atomicAdd(A.sched, A.grab);
+    for (uint32_t gj = 0; gj < A.grab; gj++) {
         const uint32_t tile32 = grab + gj;
         if (tile32 >= A.n_tiles) break;
         const int64_t tile = tile32;
@@ -525,7 +526,7 @@ int dgs_mask_level(int fn) { return fn == DGS_FN_JET ? 2 : (fn < 0 ? 0 : (fn > 3
 
 // grid of a persistent kernel: resident CTAs per SM x SMs, at most one warp per grab of work
 template <typename KernelT>
-static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
+static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles, uint32_t* grab) {
     static int cached[64];
     int dev = 0;
     cudaGetDevice(&dev);
@@ -536,7 +537,9 @@ static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles) {
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, FWD_THREADS, 0) != cudaSuccess || occ < 1) { occ = 1; (void)cudaGetLastError(); }
         cached[dev] = sms * occ;
     }
-    const int64_t need = ((int64_t)n_tiles + FWD_WARPS * FWD_GRAB - 1) / (FWD_WARPS * FWD_GRAB);
+    // few tiles per resident warp (a point shard of a multi-GPU job): grab one tile at a time, the tail is one tile long
+    *grab = ((int64_t)n_tiles >= (int64_t)16 * cached[dev] * FWD_WARPS) ? (uint32_t)FWD_GRAB : 1u;
+    const int64_t need = ((int64_t)n_tiles + FWD_WARPS * *grab - 1) / (FWD_WARPS * *grab);
     return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
 }
 
@@ -545,7 +548,9 @@ static void fwd_launch_one(const FwdArgs& a, cudaStream_t st) {
     auto kernel = dgs_forward_kernel<D, FN, CB, COUNT_ONLY>;
     DGS_PROF(COUNT_ONLY ? "forward_count_only" : "forward_kernel", st);
     cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
-    kernel<<<fwd_persistent_grid(kernel, a.n_tiles), FWD_THREADS, 0, st>>>(a);
+    FwdArgs b = a;
+    const int grid = fwd_persistent_grid(kernel, a.n_tiles, &b.grab);
+    kernel<<<grid, FWD_THREADS, 0, st>>>(b);
     DGS_NOTE_LAUNCHES(1);
 }
 

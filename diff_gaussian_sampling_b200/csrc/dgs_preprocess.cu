@@ -1019,15 +1019,18 @@ __global__ void __launch_bounds__(DGS_MASK_THREADS) dgs_l1_mask_kernel(const uin
                                                                        const float4* __restrict__ crec,
                                                                        const float* __restrict__ fine_aabb,
                                                                        const float* __restrict__ coarse_aabb, int fpcD, float tau,
-                                                                       float tau_max, M* __restrict__ masks) {
+                                                                       float tau_max, M* __restrict__ masks,
+                                                                       uint32_t* __restrict__ cflag) {
     constexpr int T = D * (D + 1) / 2;
     __shared__ float s_ctr[64][3], s_half[64][3];
     __shared__ __align__(16) float s_lean[64][D + T + ((D + T) & 1)];   // ctr[D] | h_i h_j (i <= j)
     __shared__ unsigned long long s_valid;
+    __shared__ uint32_t s_u2max;                 // max over (entry, fine tile) of h^T |C| h (float bits; >= 0, so uint order == float order)
     const int64_t tile = blockIdx.x;
     const uint32_t e0 = l1_start[tile], e1 = l1_start[tile + 1];
-    if (e0 == e1) return;
-    if (threadIdx.x == 0) s_valid = 0ull;
+    if (e0 == e1) { if (threadIdx.x == 0) cflag[tile] = 1u; return; }
+    if (threadIdx.x == 0) { s_valid = 0ull; s_u2max = 0u; }
+    float u2max = 0.f;                           // this thread's share; +inf: an entry whose extent in its own metric is unknown
     __syncthreads();
     if ((int)threadIdx.x < fpcD) {
         const int ft = threadIdx.x;
@@ -1072,6 +1075,7 @@ __global__ void __launch_bounds__(DGS_MASK_THREADS) dgs_l1_mask_kernel(const uin
 #pragma unroll
         for (int k = 0; k < T; k++) has_conic = has_conic || (rec.C[k] != 0.f);
         if (rec.rs2 < 0.f) {                    // never culled
+            u2max = INFINITY;                   // no centred form on this tile
 #pragma unroll
             for (int l = 0; l < 4; l++) m[l] = (M)valid;
         } else if (has_conic) {
@@ -1120,6 +1124,7 @@ __global__ void __launch_bounds__(DGS_MASK_THREADS) dgs_l1_mask_kernel(const uin
                     }
                     q = fmaf(r, X[i], q);
                 }
+                u2max = fmaxf(u2max, h2);
                 const float u = dgs_sqrt_approx(fmaxf(q, 0.f)) - fmaf(dgs_sqrt_approx(fmaxf(h2, 0.f)), 1.0005f, 1e-3f);
                 const M bit = (M)1 << ft;
 #pragma unroll
@@ -1134,6 +1139,7 @@ __global__ void __launch_bounds__(DGS_MASK_THREADS) dgs_l1_mask_kernel(const uin
             }
         } else {
             // ---- general path: tau_max box and sphere only (the record carries no conic) ----
+            u2max = INFINITY;                    // no centred form on this tile
             float rs2l[4], Rl[4][D < 3 ? D : 1];
 #pragma unroll
             for (int l = 0; l < 4; l++) {
@@ -1167,10 +1173,19 @@ __global__ void __launch_bounds__(DGS_MASK_THREADS) dgs_l1_mask_kernel(const uin
 #pragma unroll
         for (int l = 0; l < 4; l++) masks[(int64_t)l * n + e] = m[l];
     }
+    // the tile-centred pair form of the backward (dgs_field.cuh) is allowed on this coarse tile iff every listed
+    // Gaussian spans at most sqrt(DGS_CENTRED_U2MAX) whitened units over each fine tile's sample box
+    {
+        uint32_t b = __float_as_uint(u2max);
+        b = __reduce_max_sync(0xffffffffu, b);
+        if ((threadIdx.x & 31) == 0) atomicMax(&s_u2max, b);
+        __syncthreads();
+        if (threadIdx.x == 0) cflag[tile] = (__uint_as_float(s_u2max) * 0.72134752044448170368f <= DGS_CENTRED_U2MAX) ? 1u : 0u;
+    }
 }
 
 int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,
-                        const float* fine_aabb, const float* coarse_aabb, void* masks, cudaStream_t st) {
+                        const float* fine_aabb, const float* coarse_aabb, void* masks, uint32_t* cflag, cudaStream_t st) {
     DGS_PROF("l1_masks", st);
     const int64_t n = (int64_t)plan->n_l1;
     if (n <= 0) return 0;
@@ -1178,8 +1193,8 @@ int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const 
     const float tau = plan->tau, tau_max = plan->tau + DGS_TAU_MAX_EXTRA;
     const int f = plan->fine_per_coarse;
 #define MASK_LAUNCH(DD)                                                                                                   \
-    if (plan->mask_bytes == 8) dgs_l1_mask_kernel<DD, unsigned long long><<<nb, DGS_MASK_THREADS, 0, st>>>(l1_start, l1_ids, n, crec, fine_aabb, coarse_aabb, f, tau, tau_max, (unsigned long long*)masks); \
-    else dgs_l1_mask_kernel<DD, uint32_t><<<nb, DGS_MASK_THREADS, 0, st>>>(l1_start, l1_ids, n, crec, fine_aabb, coarse_aabb, f, tau, tau_max, (uint32_t*)masks);
+    if (plan->mask_bytes == 8) dgs_l1_mask_kernel<DD, unsigned long long><<<nb, DGS_MASK_THREADS, 0, st>>>(l1_start, l1_ids, n, crec, fine_aabb, coarse_aabb, f, tau, tau_max, (unsigned long long*)masks, cflag); \
+    else dgs_l1_mask_kernel<DD, uint32_t><<<nb, DGS_MASK_THREADS, 0, st>>>(l1_start, l1_ids, n, crec, fine_aabb, coarse_aabb, f, tau, tau_max, (uint32_t*)masks, cflag);
     if (plan->D == 1) { MASK_LAUNCH(1) } else if (plan->D == 2) { MASK_LAUNCH(2) } else { MASK_LAUNCH(3) }
 #undef MASK_LAUNCH
     DGS_NOTE_LAUNCHES(1);

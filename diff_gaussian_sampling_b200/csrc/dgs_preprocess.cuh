@@ -29,4 +29,4 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const float
 int dgs_launch_l1_cursor_init(const uint32_t* start_tmp, int n, uint32_t* start_out, uint32_t* cursor, cudaStream_t st);
 int dgs_launch_l1_sort(const dgs_plan_t* plan, const uint32_t* l1_start, uint32_t* l1_ids, uint32_t* alt, cudaStream_t st);
 int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,
-                        const float* fine_aabb, const float* coarse_aabb, void* masks, cudaStream_t st);
+                        const float* fine_aabb, const float* coarse_aabb, void* masks, uint32_t* cflag, cudaStream_t st);

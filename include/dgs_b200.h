@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DGS_ABI_VERSION 5
+#define DGS_ABI_VERSION 6
 #define DGS_ERR_BAD_ARG 10001
 #define DGS_ERR_UNSUPPORTED 10002
 #define DGS_ERR_BUFFER_TOO_SMALL 10003
@@ -100,7 +100,8 @@ typedef struct dgs_plan {
     uint64_t g_sched_off;          /* two uint32 work counters of the persistent accumulation kernels (forward, backward) */
     float    min_reach;            /* smallest narrow-axis reach sqrt(2 (tau+6) / trace(conic)) over the Gaussians (0: unknown) */
     float    reserved3;
-    uint64_t reserved2[2];
+    uint64_t g_cflag_off;          /* uint32 per coarse tile: 1 = the tile-centred pair form of the backward is numerically safe there */
+    uint64_t reserved2;
 } dgs_plan_t;
 
 int         dgs_abi_version(void);

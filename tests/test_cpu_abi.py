@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), f"{n} declared in include/dgs_b200.h but not exported"
     for n in _lib.EXPORTS:
         assert n in names, f"binding {n} is not declared in the header"
-    assert lib.dgs_abi_version() == 5
+    assert lib.dgs_abi_version() == 6
     assert lib.dgs_plan_sizeof() == ctypes.sizeof(_lib.Plan)
 
 
