@@ -33,7 +33,7 @@ class Plan(ctypes.Structure):
         ("s_plan_off", c_u64), ("s_fine_start_off", c_u64), ("s_fine_ids_off", c_u64), ("s_fine_xyz_off", c_u64),
         ("s_fine_aabb_off", c_u64), ("s_coarse_aabb_off", c_u64), ("s_tmp_off", c_u64),
         ("g_prec_off", c_u64), ("g_l1_mask_off", c_u64), ("mask_bytes", c_i32), ("samples_reused", c_i32), ("reserved", c_i32 * 2),
-        ("g_sched_off", c_u64), ("min_reach", c_f32), ("reserved3", c_f32), ("g_cflag_off", c_u64), ("reserved2", c_u64),
+        ("g_sched_off", c_u64), ("min_reach", c_f32), ("reserved3", c_f32), ("g_cflag_off", c_u64), ("s_active_off", c_u64),
     ]
 
     def as_dict(self):

@@ -190,6 +190,7 @@ static void sample_layout(dgs_plan_t* pl) {
     pl->s_fine_xyz_off = o; o = dgs_a128(o + n * 4 * pl->D);
     pl->s_fine_aabb_off = o; o = dgs_a128(o + (size_t)pl->n_fine * 32);
     pl->s_coarse_aabb_off = o; o = dgs_a128(o + (size_t)pl->n_coarse * 32);
+    pl->s_active_off = o; o = dgs_a128(o + ((size_t)pl->n_fine + 1) * 4);
     pl->s_tmp_off = o; o += sample_tmp_layout(pl).total;
     pl->sample_binning_bytes = o + 128;
 }
@@ -502,7 +503,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
             if (rc) return rc;
             rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
             if (rc) return rc;
-            rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
+            rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, (uint32_t*)(sb + plan->s_active_off), st);
             if (rc) return rc;
             rc = dgs_sort_pairs_u64_prehist(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, N, 32, 32 + plan->sort_bits,
                                             hist, hist_scan_tmp, st);
@@ -517,7 +518,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
             if (rc) return rc;
             rc = dgs_launch_fine_scatter(samples_dev, plan, tile_of, rank_of, fine_start, fine_ids, fine_xyz, st);
             if (rc) return rc;
-            rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, st);
+            rc = dgs_launch_tile_aabb(plan, fine_xyz, fine_start, fine_aabb, coarse_aabb, (uint32_t*)(sb + plan->s_active_off), st);
             if (rc) return rc;
             // public sorted sample list: stable sort on the cell bits == sort on bits [0, 32+bit)
             rc = dgs_sort_pairs_u64(pa.keys_unsorted, pa.list_unsorted, pa.keys, pa.list, (uint64_t*)(stmp + tl.alt_keys),

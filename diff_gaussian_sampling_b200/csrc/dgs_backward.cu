@@ -66,6 +66,7 @@ struct BwdArgs {
     const float* fine_aabb; const float* coarse_aabb;
     float* dmeans; float* dvalues; float* dconics;
     uint32_t* sched;                              // work counter of this launch (zeroed by the launcher)
+    const uint32_t* active;                       // [0] = number of fine tiles that hold samples, [1..] their ids (dgs_tile_aabb_kernel)
     int64_t N;
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
@@ -604,16 +605,17 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     uint32_t* qG = qF + BWD_QF;
     uint32_t* qR = qG + BWD_QG;
     // persistent warps pulling fine tiles from a global counter (see dgs_forward.cu)
+    const uint32_t n_act = A.active[0];
     uint32_t nx = 0;
     if (lane == 0) nx = atomicAdd(A.sched, A.grab);
     for (;;) {
     const uint32_t grab = __shfl_sync(0xffffffffu, nx, 0);
-    if (grab >= A.n_tiles) break;
+    if (grab >= n_act) break;
     if (lane == 0) nx = atomicAdd(A.sched, A.grab);
     for (uint32_t gj = 0; gj < A.grab; gj++) {
         const uint32_t tile32 = grab + gj;
-        if (tile32 >= A.n_tiles) break;
-        const int64_t tile = tile32;
+        if (tile32 >= n_act) break;
+        const int64_t tile = A.active[1 + tile32];
         const int64_t coarse = tile / A.fpcD;
         const int ft = (int)(tile - coarse * A.fpcD);
         const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
@@ -854,7 +856,7 @@ int dgs_mask_level(int fn);
 int dgs_launch_pack(const float* means, const float* conics, const float* values, int C, int64_t P, int D, float* prec, cudaStream_t st);
 
 template <typename KernelT>
-static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles, uint32_t* grab) {
+static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles, int64_t n_samples, uint32_t* grab) {
     static int cached[64];
     int dev = 0;
     cudaGetDevice(&dev);
@@ -866,7 +868,7 @@ static int bwd_persistent_grid(KernelT kernel, uint32_t n_tiles, uint32_t* grab)
         cached[dev] = sms * occ;
     }
     // few tiles per resident warp (a point shard of a multi-GPU job): grab one tile at a time, the tail is one tile long
-    *grab = ((int64_t)n_tiles >= (int64_t)16 * cached[dev] * BWD_WARPS) ? (uint32_t)BWD_GRAB : 1u;
+    *grab = (n_samples / 128 >= (int64_t)16 * cached[dev] * BWD_WARPS) ? (uint32_t)BWD_GRAB : 1u;   // ~ non-empty tiles per warp
     const int64_t need = ((int64_t)n_tiles + BWD_WARPS * *grab - 1) / (BWD_WARPS * *grab);
     return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
 }
@@ -877,7 +879,7 @@ static void bwd_launch_one_c(const BwdArgs& a, cudaStream_t st) {
     DGS_PROF("backward_kernel", st);
     cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
     BwdArgs b = a;
-    const int grid = bwd_persistent_grid(kernel, a.n_tiles, &b.grab);
+    const int grid = bwd_persistent_grid(kernel, a.n_tiles, a.N, &b.grab);
     kernel<<<grid, BWD_THREADS, 0, st>>>(b);
     DGS_NOTE_LAUNCHES(1);
 }
@@ -937,6 +939,7 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.fine_xyz = (const float*)(sbuf + plan->s_fine_xyz_off);
     a.fine_aabb = (const float*)(sbuf + plan->s_fine_aabb_off);
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
+    a.active = (const uint32_t*)(sbuf + plan->s_active_off);
     a.dmeans = dmeans; a.dvalues = dvalues; a.dconics = dconics;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
     a.sched = (uint32_t*)(gbuf + plan->g_sched_off) + 1;     // the forward's counter is word 0

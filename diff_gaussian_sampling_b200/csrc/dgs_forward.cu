@@ -54,6 +54,7 @@ struct FwdArgs {
     float* out1; float* out2;                     // jet: derivative (N, D, C) and Hessian (N, D, D, C); `out` is the value
     unsigned long long* pair_counter;
     uint32_t* sched;                              // work counter of this launch (zeroed by the launcher)
+    const uint32_t* active;                       // [0] = number of fine tiles that hold samples, [1..] their ids (dgs_tile_aabb_kernel)
     int64_t N;
     int C, ch0, fpcD;
     uint32_t n_tiles;                             // n_coarse * fpcD
@@ -242,16 +243,17 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
     // issued before the current tiles are worked on, so its latency is hidden).  Tiles of one coarse tile are adjacent, so
     // the warps of an SM mostly share coarse lists in L1/L2; no static assignment means no tail (round 1: one CTA per
     // coarse tile, 12 % of the SM cycles idle at the end of the forward kernel).
+    const uint32_t n_act = A.active[0];
     uint32_t nx = 0;                                   // lane 0: the grab in flight
     if (lane == 0) nx = atomicAdd(A.sched, A.grab);
     for (;;) {
     const uint32_t grab = __shfl_sync(0xffffffffu, nx, 0);
-    if (grab >= A.n_tiles) break;
+    if (grab >= n_act) break;
     if (lane == 0) nx = atomicAdd(A.sched, A.grab);
     for (uint32_t gj = 0; gj < A.grab; gj++) {
         const uint32_t tile32 = grab + gj;
-        if (tile32 >= A.n_tiles) break;
-        const int64_t tile = tile32;
+        if (tile32 >= n_act) break;
+        const int64_t tile = A.active[1 + tile32];
         const int64_t coarse = tile / A.fpcD;
         const int ft = (int)(tile - coarse * A.fpcD);
         const uint32_t s0 = A.fine_start[tile], s1 = A.fine_start[tile + 1];
@@ -526,7 +528,7 @@ int dgs_mask_level(int fn) { return fn == DGS_FN_JET ? 2 : (fn < 0 ? 0 : (fn > 3
 
 // grid of a persistent kernel: resident CTAs per SM x SMs, at most one warp per grab of work
 template <typename KernelT>
-static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles, uint32_t* grab) {
+static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles, int64_t n_samples, uint32_t* grab) {
     static int cached[64];
     int dev = 0;
     cudaGetDevice(&dev);
@@ -538,7 +540,7 @@ static int fwd_persistent_grid(KernelT kernel, uint32_t n_tiles, uint32_t* grab)
         cached[dev] = sms * occ;
     }
     // few tiles per resident warp (a point shard of a multi-GPU job): grab one tile at a time, the tail is one tile long
-    *grab = ((int64_t)n_tiles >= (int64_t)16 * cached[dev] * FWD_WARPS) ? (uint32_t)FWD_GRAB : 1u;
+    *grab = (n_samples / 128 >= (int64_t)16 * cached[dev] * FWD_WARPS) ? (uint32_t)FWD_GRAB : 1u;   // ~ non-empty tiles per warp
     const int64_t need = ((int64_t)n_tiles + FWD_WARPS * *grab - 1) / (FWD_WARPS * *grab);
     return (int)(need < cached[dev] ? (need < 1 ? 1 : need) : cached[dev]);
 }
@@ -549,7 +551,7 @@ static void fwd_launch_one(const FwdArgs& a, cudaStream_t st) {
     DGS_PROF(COUNT_ONLY ? "forward_count_only" : "forward_kernel", st);
     cudaMemsetAsync(a.sched, 0, sizeof(uint32_t), st);
     FwdArgs b = a;
-    const int grid = fwd_persistent_grid(kernel, a.n_tiles, &b.grab);
+    const int grid = fwd_persistent_grid(kernel, a.n_tiles, a.N, &b.grab);
     kernel<<<grid, FWD_THREADS, 0, st>>>(b);
     DGS_NOTE_LAUNCHES(1);
 }
@@ -599,6 +601,7 @@ int dgs_launch_forward(const dgs_plan_t* plan, int fn, int C, const float* means
     a.fine_xyz = (const float*)(sbuf + plan->s_fine_xyz_off);
     a.fine_aabb = (const float*)(sbuf + plan->s_fine_aabb_off);
     a.coarse_aabb = (const float*)(sbuf + plan->s_coarse_aabb_off);
+    a.active = (const uint32_t*)(sbuf + plan->s_active_off);
     a.out = out; a.out1 = out_derivative; a.out2 = out_hessian; a.pair_counter = pair_counter;
     a.N = plan->N; a.C = C; a.ch0 = 0; a.fpcD = plan->fine_per_coarse;
     a.sched = sched_scratch ? sched_scratch : (uint32_t*)(gbuf + plan->g_sched_off);

@@ -500,12 +500,20 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_fine_scatter_kernel(const flo
 
 // One CTA per coarse tile, one warp per fine tile: bounding boxes of the samples actually in
 // each tile.  Box layout (8 floats): lo[3], hi[3], count (as int), unused.  Empty: lo=+inf, hi=-inf.
+// Also appends the coarse tile's non-empty fine tiles (in order) to the work list active[1 + ...] (count in active[0],
+// zeroed by the launcher) that the persistent accumulation kernels walk: a point shard of a multi-GPU job occupies a
+// fraction of the tile grid, and warps spinning through empty tiles serialise on the single work counter (measured:
+// forward 0.40 ms for a 1/8 slab of cfg2 against 0.21 ms for an eighth of the full grid).
 template <int D>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float* __restrict__ fine_xyz, int64_t N,
                                                                     const uint32_t* __restrict__ fine_start, int fpcD,
-                                                                    float* __restrict__ fine_aabb, float* __restrict__ coarse_aabb) {
+                                                                    float* __restrict__ fine_aabb, float* __restrict__ coarse_aabb,
+                                                                    uint32_t* __restrict__ active) {
     __shared__ float s_lo[DGS_THREADS / 32][3], s_hi[DGS_THREADS / 32][3];
     __shared__ uint32_t s_n[DGS_THREADS / 32];
+    __shared__ unsigned long long s_nonempty;
+    if (threadIdx.x == 0) s_nonempty = 0ull;
+    __syncthreads();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t coarse = blockIdx.x;
     float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -533,6 +541,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float*
             chi[d] = fmaxf(chi[d], hi[d]);
         }
         cn += s1 - s0;
+        if (lane == 0 && s1 > s0) atomicOr(&s_nonempty, 1ull << ft);
         if (lane == 0) {
             float* o = fine_aabb + tile * 8;
             o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2]; o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
@@ -555,6 +564,15 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float*
         float* o = coarse_aabb + coarse * 8;
         o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2]; o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
         o[6] = __int_as_float((int)n); o[7] = 0.f;
+        unsigned long long ne = s_nonempty;            // fpcD <= 64
+        if (ne) {
+            uint32_t pos = 1u + atomicAdd(active, (uint32_t)__popcll(ne));
+            while (ne) {
+                const int ft = __ffsll((long long)ne) - 1;
+                ne &= ne - 1;
+                active[pos++] = (uint32_t)(coarse * fpcD + ft);
+            }
+        }
     }
 }
 
@@ -668,13 +686,15 @@ int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const 
 }
 
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
-                         float* coarse_aabb, cudaStream_t st) {
+                         float* coarse_aabb, uint32_t* active, cudaStream_t st) {
     DGS_PROF("tile_aabb", st);
     if (plan->n_coarse <= 0) return 0;
+    DGS_REQUIRE(plan->fine_per_coarse <= 64, DGS_ERR_UNSUPPORTED, "more than 64 fine tiles per coarse tile");
+    DGS_CUDA(cudaMemsetAsync(active, 0, sizeof(uint32_t), st));
     const int nb = plan->n_coarse;
-    if (plan->D == 1) dgs_tile_aabb_kernel<1><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
-    else if (plan->D == 2) dgs_tile_aabb_kernel<2><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
-    else dgs_tile_aabb_kernel<3><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb);
+    if (plan->D == 1) dgs_tile_aabb_kernel<1><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active);
+    else if (plan->D == 2) dgs_tile_aabb_kernel<2><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active);
+    else dgs_tile_aabb_kernel<3><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active);
     DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;

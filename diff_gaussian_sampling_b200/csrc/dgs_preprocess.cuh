@@ -22,7 +22,7 @@ int dgs_launch_ranges_from_hist(const uint32_t* hist_scanned, int nd, int n_chun
 int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const uint32_t* tile_of, const uint32_t* rank_of,
                             const uint32_t* fine_start, uint32_t* fine_ids, float* fine_xyz, cudaStream_t st);
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
-                         float* coarse_aabb, cudaStream_t st);
+                         float* coarse_aabb, uint32_t* active, cudaStream_t st);
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
                   const dgs_plan_t* plan, const float* coarse_aabb, const void* sample_ranges, uint32_t* tile_cnt,
                   unsigned long long* n1bits, uint32_t* ids, cudaStream_t st);

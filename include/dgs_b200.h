@@ -101,7 +101,7 @@ typedef struct dgs_plan {
     float    min_reach;            /* smallest narrow-axis reach sqrt(2 (tau+6) / trace(conic)) over the Gaussians (0: unknown) */
     float    reserved3;
     uint64_t g_cflag_off;          /* uint32 per coarse tile: 1 = the tile-centred pair form of the backward is numerically safe there */
-    uint64_t reserved2;
+    uint64_t s_active_off;         /* uint32 count + the ids of the fine tiles that hold samples (the accumulation kernels' work list) */
 } dgs_plan_t;
 
 int         dgs_abi_version(void);
