@@ -350,7 +350,12 @@ def run_ours(args, rank, world, local_rank):
     e2e = None
     if not args.no_e2e:
         from diff_gaussian_sampling_b200.host_pipeline import HostPipeline
-        grads_host = torch.empty(P * (D + C + T), dtype=torch.float32).pin_memory()
+        # N > 1: every rank reads back its 1/N slice of the all-reduced flat gradient (together the ranks return the whole
+        # gradient once, like N = 1) plus the loss — not N copies of the same 24 MB through one host
+        n_grad = P * (D + C + T)
+        g_per = (n_grad + world - 1) // world
+        g_lo, g_hi = min(rank * g_per, n_grad), min((rank + 1) * g_per, n_grad)
+        grads_host = torch.empty(g_hi - g_lo, dtype=torch.float32).pin_memory()
         loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
         pipe = HostPipeline(dev, depth=3)
         widths = [("means", D), ("values", C), ("covariances", T), ("conics", T)]
@@ -375,7 +380,7 @@ def run_ours(args, rank, world, local_rank):
                 tt[k] = full[o:o + P * w].view(P, w)
                 o += P * w
             flat, out = step(tt)
-            return flat, (out * dout).sum().reshape(1)
+            return flat[g_lo:g_hi], (out * dout).sum().reshape(1)
 
         def e2e_run(k):
             return pipe.run((e2e_batch for _ in range(k)), e2e_step, lambda i: (grads_host, loss_host))
@@ -795,7 +800,7 @@ def main():
                            "h2d_gbps_per_rank_all_ranks_copying": {"min": float(mn[1]), "mean": float(cnt[1]) / world},
                            "staging": "HostPipeline depth 3: the H2D copies of the next steps overlap step i; K steps timed as "
                                       "one region, pipeline fill included; bytes are per rank"
-                                      + ("; each rank uploads 1/N of the Gaussian parameters, one all_gather completes them" if world > 1 else "")}
+                                      + ("; each rank uploads 1/N of the Gaussian parameters (one all_gather completes them) and reads back 1/N of the all-reduced gradient" if world > 1 else "")}
         if not args.no_cpu_baseline and world == 1:   # reported at N=1 only
             try:
                 line["cpu_baseline"] = cpu_port_baseline(args.workload, ({1: 1024, 2: 32, 3: 10}[D] if P >= 1_000_000 else min(WORKLOADS[args.workload][2], 256)))   # ~1e9 pairs: 10-30 s of CPU work
