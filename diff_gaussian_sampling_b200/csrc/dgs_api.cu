@@ -190,7 +190,7 @@ static void sample_layout(dgs_plan_t* pl) {
     pl->s_fine_xyz_off = o; o = dgs_a128(o + n * 4 * pl->D);
     pl->s_fine_aabb_off = o; o = dgs_a128(o + (size_t)pl->n_fine * 32);
     pl->s_coarse_aabb_off = o; o = dgs_a128(o + (size_t)pl->n_coarse * 32);
-    pl->s_active_off = o; o = dgs_a128(o + ((size_t)pl->n_fine + 1) * 4);
+    pl->s_active_off = o; o = dgs_a128(o + ((size_t)pl->n_fine + 1) * 4 + 64);   // + the box of this call's samples (dgs_sbox_of)
     pl->s_tmp_off = o; o += sample_tmp_layout(pl).total;
     pl->sample_binning_bytes = o + 128;
 }
@@ -534,7 +534,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_count(dgs_p
     uint32_t* l1_start_tmp = (uint32_t*)(stmp + tl.l1_start);
     DGS_CUDA(cudaMemsetAsync(l1_cnt, 0, ((size_t)plan->n_coarse + 1) * 4, st));
     DGS_CUDA(cudaMemcpyAsync(stmp + tl.sranges, sample_ranges_dev, (size_t)plan->ranges_bytes, cudaMemcpyDeviceToDevice, st));
-    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, stmp + tl.sranges, l1_cnt,
+    rc = dgs_launch_l1(false, means_dev, radii_dev, crec, crecR, plan, coarse_aabb, dgs_sbox_of(plan, sb), stmp + tl.sranges, l1_cnt,
                        (unsigned long long*)(g + gl.n1bits), nullptr, st);
     if (rc) return rc;
     rc = dgs_exclusive_scan_u32(l1_cnt, l1_start_tmp, (int64_t)plan->n_coarse + 1, stmp + tl.l1_scan_tmp, (uint32_t*)&hdr->n_l1, st);
@@ -595,7 +595,7 @@ extern "C" __attribute__((visibility("default"))) int dgs_preprocess_bin(const d
     rc = dgs_launch_l1_cursor_init((const uint32_t*)(stmp + stl.l1_start), plan->n_coarse + 1, l1_start, cursor, st);
     if (rc) return rc;
     if (plan->n_l1 > 0) {
-        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, stmp + stl.sranges, cursor,
+        rc = dgs_launch_l1(true, means_dev, radii_dev, crec, (const float*)(g + gl.crecR), plan, coarse_aabb, dgs_sbox_of(plan, sb), stmp + stl.sranges, cursor,
                            (unsigned long long*)(g + gl.n1bits), l1_ids, st);
         if (rc) return rc;
         rc = dgs_launch_l1_sort(plan, l1_start, l1_ids, (uint32_t*)(tmp + tl.l1_alt), st);

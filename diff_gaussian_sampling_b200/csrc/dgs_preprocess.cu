@@ -508,7 +508,7 @@ template <int D>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float* __restrict__ fine_xyz, int64_t N,
                                                                     const uint32_t* __restrict__ fine_start, int fpcD,
                                                                     float* __restrict__ fine_aabb, float* __restrict__ coarse_aabb,
-                                                                    uint32_t* __restrict__ active) {
+                                                                    uint32_t* __restrict__ active, uint32_t sbox_word) {
     __shared__ float s_lo[DGS_THREADS / 32][3], s_hi[DGS_THREADS / 32][3];
     __shared__ uint32_t s_n[DGS_THREADS / 32];
     __shared__ unsigned long long s_nonempty;
@@ -566,6 +566,12 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_tile_aabb_kernel(const float*
         o[6] = __int_as_float((int)n); o[7] = 0.f;
         unsigned long long ne = s_nonempty;            // fpcD <= 64
         if (ne) {
+            uint32_t* sbox = active + sbox_word;       // box of all samples of this call (dgs_sbox_of)
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                atomicMin(&sbox[d], dgs_f2ord(lo[d]));
+                atomicMin(&sbox[3 + d], ~dgs_f2ord(hi[d]));
+            }
             uint32_t pos = 1u + atomicAdd(active, (uint32_t)__popcll(ne));
             while (ne) {
                 const int ft = __ffsll((long long)ne) - 1;
@@ -691,10 +697,12 @@ int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const ui
     if (plan->n_coarse <= 0) return 0;
     DGS_REQUIRE(plan->fine_per_coarse <= 64, DGS_ERR_UNSUPPORTED, "more than 64 fine tiles per coarse tile");
     DGS_CUDA(cudaMemsetAsync(active, 0, sizeof(uint32_t), st));
+    const uint32_t sbox_word = (uint32_t)(((size_t)plan->n_fine + 1 + 3) & ~(size_t)3);      // == dgs_sbox_of
+    DGS_CUDA(cudaMemsetAsync(active + sbox_word, 0xff, 8 * sizeof(uint32_t), st));
     const int nb = plan->n_coarse;
-    if (plan->D == 1) dgs_tile_aabb_kernel<1><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active);
-    else if (plan->D == 2) dgs_tile_aabb_kernel<2><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active);
-    else dgs_tile_aabb_kernel<3><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active);
+    if (plan->D == 1) dgs_tile_aabb_kernel<1><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active, sbox_word);
+    else if (plan->D == 2) dgs_tile_aabb_kernel<2><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active, sbox_word);
+    else dgs_tile_aabb_kernel<3><<<nb, DGS_THREADS, 0, st>>>(fine_xyz, plan->N, fine_start, plan->fine_per_coarse, fine_aabb, coarse_aabb, active, sbox_word);
     DGS_NOTE_LAUNCHES(1);
     DGS_LAUNCH_CHECK();
     return 0;
@@ -721,7 +729,8 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
                                                              const float4* __restrict__ crec, const float* __restrict__ crecR,
                                                              float two_tau, int64_t P, DgsGrid G, int cpc,
                                                              int T1, int blocks,
-                                                             const float* __restrict__ coarse_aabb, const uint2* __restrict__ sample_ranges,
+                                                             const float* __restrict__ coarse_aabb, const uint32_t* __restrict__ sbox,
+                                                             const uint2* __restrict__ sample_ranges,
                                                              uint32_t* __restrict__ tile_cnt,
                                                              unsigned long long* __restrict__ n1bits,
                                                              uint32_t* __restrict__ ids) {
@@ -755,6 +764,24 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
         const DgsCullRecView rec = dgs_crec_load<D>(crec, i);
         const float recR[3] = {crecR[i * 3], crecR[i * 3 + 1], crecR[i * 3 + 2]};
         const bool always = rec.rs2 < 0.f;
+        // A Gaussian whose tau_max box (or a period-2 image of it) misses the box of ALL samples of this call cannot pass
+        // the box test of any tile: skip it before any cell is enumerated.  On a point shard of a multi-GPU job that is
+        // most Gaussians (the replicated Gaussian-side passes are what limits strong scaling).
+        bool reach_any = true;
+        if (!always) {
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const float slo = dgs_ord2f(__ldg(sbox + d)), shi = dgs_ord2f(~__ldg(sbox + 3 + d));
+                const float R = recR[d] * 1.0001f + 1e-5f;
+                bool ov = false;
+#pragma unroll
+                for (int k = -1; k <= 1; k++) {
+                    const float m = rec.mu[d] + 2.0f * (float)k;
+                    ov = ov || ((m + R >= slo) && (m - R <= shi));
+                }
+                reach_any = reach_any && ov;
+            }
+        }
         // The count pass remembers the verdicts of the first 63 enumerated tiles in a bitmask, so that the
         // emit pass (same enumeration) does not reload the tile boxes and repeat the tests.
         if (EMIT) bits = n1bits[i];
@@ -783,7 +810,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
             }
             ci++;
         };
-        dgs_for_each_cell<D>(p, r, G, [&](int cell) {
+        if (reach_any) dgs_for_each_cell<D>(p, r, G, [&](int cell) {
             if (cell >= G.n_ranges) return;
             // a cell without samples (point shard of a multi-GPU job: most of them) has no tile to list the Gaussian in
             const uint2 sr = __ldg(sample_ranges + cell);
@@ -861,7 +888,7 @@ __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __rest
 }
 
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
-                  const dgs_plan_t* plan, const float* coarse_aabb, const void* sample_ranges, uint32_t* tile_cnt,
+                  const dgs_plan_t* plan, const float* coarse_aabb, const uint32_t* sbox, const void* sample_ranges, uint32_t* tile_cnt,
                   unsigned long long* n1bits, uint32_t* ids, cudaStream_t st) {
     DGS_PROF(emit ? "l1_emit" : "l1_count", st);
     const int64_t P = plan->P;
@@ -873,8 +900,8 @@ int dgs_launch_l1(bool emit, const float* means, const float* radii, const float
     const int cpc = plan->coarse_per_cell;
     const float two_tau = 2.0f * (plan->tau + DGS_TAU_MAX_EXTRA);
 #define L1_LAUNCH(DD)                                                                                                         \
-    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, (const uint2*)sample_ranges, tile_cnt, n1bits, ids); \
-    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, (const uint2*)sample_ranges, tile_cnt, n1bits, ids);
+    if (emit) dgs_l1_kernel<DD, true><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, sbox, (const uint2*)sample_ranges, tile_cnt, n1bits, ids); \
+    else dgs_l1_kernel<DD, false><<<nb, DGS_THREADS, 0, st>>>(means, radii, crec, crecR, two_tau, P, G, cpc, plan->T1, plan->blocks, coarse_aabb, sbox, (const uint2*)sample_ranges, tile_cnt, n1bits, ids);
     if (plan->D == 1) { L1_LAUNCH(1) } else if (plan->D == 2) { L1_LAUNCH(2) } else { L1_LAUNCH(3) }
 #undef L1_LAUNCH
     DGS_NOTE_LAUNCHES(1);

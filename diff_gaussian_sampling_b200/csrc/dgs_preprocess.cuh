@@ -24,9 +24,15 @@ int dgs_launch_fine_scatter(const float* samples, const dgs_plan_t* plan, const 
 int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const uint32_t* fine_start, float* fine_aabb,
                          float* coarse_aabb, uint32_t* active, cudaStream_t st);
 int dgs_launch_l1(bool emit, const float* means, const float* radii, const float4* crec, const float* crecR,
-                  const dgs_plan_t* plan, const float* coarse_aabb, const void* sample_ranges, uint32_t* tile_cnt,
+                  const dgs_plan_t* plan, const float* coarse_aabb, const uint32_t* sbox, const void* sample_ranges, uint32_t* tile_cnt,
                   unsigned long long* n1bits, uint32_t* ids, cudaStream_t st);
 int dgs_launch_l1_cursor_init(const uint32_t* start_tmp, int n, uint32_t* start_out, uint32_t* cursor, cudaStream_t st);
 int dgs_launch_l1_sort(const dgs_plan_t* plan, const uint32_t* l1_start, uint32_t* l1_ids, uint32_t* alt, cudaStream_t st);
 int dgs_launch_l1_masks(const dgs_plan_t* plan, const uint32_t* l1_start, const uint32_t* l1_ids, const float4* crec,
                         const float* fine_aabb, const float* coarse_aabb, void* masks, uint32_t* cflag, cudaStream_t st);
+
+// Box of THIS call's samples (exact: the union of the coarse-tile boxes), kept behind the work list in the sample binning
+// buffer: 3 ordered-int minima, then 3 bit-inverted ordered-int maxima (both reduced with atomicMin from 0xffffffff).
+static inline uint32_t* dgs_sbox_of(const dgs_plan_t* plan, void* sample_binning) {
+    return (uint32_t*)((uint8_t*)sample_binning + plan->s_active_off) + (((size_t)plan->n_fine + 1 + 3) & ~(size_t)3);
+}
