@@ -39,6 +39,11 @@
 #ifndef BWD_TUNED_3D
 #define BWD_TUNED_3D 0   // same for D == 3 (0 = ptxas' choice, 95 registers; 4, 6, 7 measured no better)
 #endif
+#ifndef BWD_CEN_UNROLL
+#define BWD_CEN_UNROLL 2   // sample-pair iterations of the tile-centred loop per trip for D <= 2 (cfg2 bwd 2.36 -> 2.29 ms; D == 3 stays at 1:
+                           // 124 registers and 10.29 -> 10.40 ms with 2; profiles/r02_sweep_backward_variants.jsonl: v1 = BWD_TUNED_3D 6, v2 = 5,
+                           // v3 = this, v4 = BWD_TUNED 6, v5 = 8, v6 = v3 + v4)
+#endif
 #ifndef BWD_MOMENTS
 #define BWD_MOMENTS 1   // derivative orders, one channel: accumulate C- and v-free moments (bwd_pair_moments)
 #endif
@@ -304,6 +309,8 @@ __device__ __forceinline__ void bwd_batch_centred(const BwdArgs& A, const float*
 #pragma unroll
         for (int k = 0; k < T; k++) S22[g][k] = make_float2(0.f, 0.f);
     }
+    constexpr int CEN_UNROLL = D <= 2 ? BWD_CEN_UNROLL : 1;
+#pragma unroll CEN_UNROLL
     for (int j = 0; j < npair; j++) {
         float f[(NL + 3) / 4 * 4];
 #pragma unroll
