@@ -224,6 +224,47 @@ __device__ __forceinline__ void fwd_flush_fast(int s_eff, const float* __restric
     }
 }
 
+// Pipelined path (gaussian, one channel): the lane's samples live as PAIRS for the whole tile pass — nx2[p] = -(x_2p, x_2p+1)
+// per axis and the accumulator pair a2[p] — so the loop below contains packed instructions only: no pair is assembled or
+// taken apart per record (a scalar FMA-pipe instruction such as IMAD.MOV inside a packed loop costs as much as a packed one,
+// profiles/r02_mb_packed_scalar_mix.jsonl).  An odd last row is paired with a zero sample whose result is never stored.
+template <int D, int SP, int STRIDE>
+__device__ __forceinline__ void fwd_eval_packed(const float* __restrict__ sF, int nf, const float2 (&nx2)[4][D], float2 (&a2)[4]) {
+    constexpr int T = D * (D + 1) / 2;
+    const float* rp = sF;
+    for (int k = 0; k < nf; k++, rp += STRIDE) {
+        float r[(D + T + 1 + 1) / 2 * 2];
+#pragma unroll
+        for (int q = 0; q < (D + T + 1 + 1) / 2; q++) {
+            const float2 v = *(const float2*)(rp + q * 2);
+            r[q * 2] = v.x; r[q * 2 + 1] = v.y;
+        }
+        float2 U2[T];
+#pragma unroll
+        for (int t = 0; t < T; t++) U2[t] = dgs_bc2(r[D + t]);
+        const float2 val2 = dgs_bc2(r[D + T]);
+#pragma unroll
+        for (int p = 0; p < SP; p++) {
+            float2 X[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) X[d] = __fadd2_rn(dgs_bc2(r[d]), nx2[p][d]);
+            const float2 t2 = dgs_white_t2<D>(X, U2);
+            const float2 G = make_float2(dgs_ex2(-t2.x), dgs_ex2(-t2.y));
+            a2[p] = __ffma2_rn(val2, G, a2[p]);
+        }
+    }
+}
+template <int D, int STRIDE>
+__device__ __forceinline__ void fwd_flush_packed(int sp_eff, const float* __restrict__ sF, int nf, const float2 (&nx2)[4][D],
+                                                 float2 (&a2)[4]) {
+    switch (sp_eff) {
+        case 1: fwd_eval_packed<D, 1, STRIDE>(sF, nf, nx2, a2); break;
+        case 2: fwd_eval_packed<D, 2, STRIDE>(sF, nf, nx2, a2); break;
+        case 3: fwd_eval_packed<D, 3, STRIDE>(sF, nf, nx2, a2); break;
+        default: fwd_eval_packed<D, 4, STRIDE>(sF, nf, nx2, a2); break;
+    }
+}
+
 template <int D, int FN, int CB, bool COUNT_ONLY>
 __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? FWD_TUNED : FWD_TUNED_3D) : FWD_MINB) dgs_forward_kernel(const FwdArgs A) {
     using K = FwdCfg<D, FN, CB>;
@@ -295,6 +336,17 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                 // batch of arithmetic; the (mask, id) words of the next 64 list entries are loaded one chunk ahead. ----
                 float* raw = sF;
                 int nq = 0, cnt_prev = 0, cur = 0;
+                static_assert(SMAX <= 8, "at most four sample pairs per lane");
+                float2 nx2[4][D], a2[4];
+#pragma unroll
+                for (int p2 = 0; p2 < 4; p2++) {
+#pragma unroll
+                    for (int d = 0; d < D; d++)
+                        nx2[p2][d] = make_float2(2 * p2 < SMAX ? -x[2 * p2 < SMAX ? 2 * p2 : 0][d] : 0.f,
+                                                 2 * p2 + 1 < SMAX ? -x[2 * p2 + 1 < SMAX ? 2 * p2 + 1 : 0][d] : 0.f);
+                    a2[p2] = make_float2(0.f, 0.f);
+                }
+                const int sp_eff = (s_eff + 1) >> 1;
                 auto process = [&](const float* buf, int cnt) {
                     // wrap / far Gaussians (rare: tiles at the torus seam) go through the literal path; their value is
                     // zeroed in the fast record, which is then evaluated harmlessly
@@ -326,8 +378,16 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         }
                         __syncwarp();
                     }
-                    fwd_flush_fast<D, FN, CB, PW>(s_eff, buf, cnt, x, acc);
-                    if (balG) fwd_eval_general<D, FN, CB>(sG, __popc(balG), s_eff, x, acc);
+                    fwd_flush_packed<D, PW>(sp_eff, buf, cnt, nx2, a2);
+                    if (balG) {
+                        // the literal path accumulates into the scalar accumulators: fold them into the pairs afterwards
+                        fwd_eval_general<D, FN, CB>(sG, __popc(balG), s_eff, x, acc);
+#pragma unroll
+                        for (int i = 0; i < SMAX; i++) {
+                            if (i & 1) a2[i >> 1].y += acc[i][0][0]; else a2[i >> 1].x += acc[i][0][0];
+                            acc[i][0][0] = 0.f;
+                        }
+                    }
                     __syncwarp();
                 };
                 // chunk prefetch registers
@@ -386,6 +446,8 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         break;
                     }
                 }
+#pragma unroll
+                for (int i = 0; i < SMAX; i++) acc[i][0][0] = (i & 1) ? a2[i >> 1].y : a2[i >> 1].x;
                 goto tile_pass_done;
               }
             }
