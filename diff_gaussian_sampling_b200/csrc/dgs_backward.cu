@@ -59,6 +59,15 @@
 #define BWD_QG 64    // general-id queue slots per warp
 #define BWD_QRAW 96  // raw survivor-id queue slots per warp (< 32 left over + 64 new)
 #define BWD_EXACT_BIT 0x80000000u
+// D == 3 (no reference arm to reproduce bit for bit): a Gaussian whose displacement lies in (1, 2) or (-2, -1) on an axis for
+// EVERY sample of the tile is evaluated on the fast path with its mean shifted by -/+ 2 on that axis (see dgs_forward.cu);
+// the shift code (2 bits per axis: 1 = -2, 2 = +2) rides in bits 24..29 of the queue entry when P < 2^24.
+#define BWD_SHIFT_LSB 24
+#define BWD_ID_MASK_SHIFT 0x00ffffffu
+__device__ __forceinline__ float bwd_shift_of(uint32_t ent, int d) {
+    const uint32_t c = (ent >> (BWD_SHIFT_LSB + 2 * d)) & 3u;
+    return c == 1u ? -2.0f : (c == 2u ? 2.0f : 0.f);
+}
 
 struct BwdArgs {
     const float* values; const float* conics; const float* dout;
@@ -78,6 +87,7 @@ struct BwdArgs {
     uint32_t grab;                                // fine tiles per grab of the work counter (BWD_GRAB, or 1 when a rank has few tiles per warp: shorter tail)
     float t_max;                                  // tau of this function level x log2(e): |U X|^2 beyond it is culled
     int centred;                                  // fn 0: second moments about the tile centre are numerically safe (launcher)
+    int shift_ok;                                 // D == 3 and P < 2^24: queue entries carry a per-axis mean shift code in bits 24..29
 };
 
 template <int D, int FN, int CB>
@@ -281,20 +291,25 @@ __device__ __forceinline__ void bwd_batch_centred(const BwdArgs& A, const float*
     constexpr int T = K::T, PRW = K::PRW;
     constexpr int NL = 2 * (D + 1 + T);            // floats of a pair record the fast path reads
     constexpr int PW = DGS_PREC_W(D);
-    uint32_t id[NG];
+    uint32_t id[NG], ent[NG];
     bool valid[NG];
     float Ug[NG][T], nb[NG][D];
 #pragma unroll
     for (int g = 0; g < NG; g++) {
         const int qi = lane + 32 * g;
         valid[g] = qi < count;
-        id[g] = queue[valid[g] ? qi : 0] & ~BWD_EXACT_BIT;
+        ent[g] = queue[valid[g] ? qi : 0];
+        id[g] = (D == 3 && A.shift_ok) ? (ent[g] & BWD_ID_MASK_SHIFT) : (ent[g] & ~BWD_EXACT_BIT);
         const float4* p4 = (const float4*)(A.prec + (int64_t)id[g] * PW);
         float pr[PW];
 #pragma unroll
         for (int q = 0; q < PW / 4; q++) {
             const float4 v = __ldg(p4 + q);
             pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
+        }
+        if (D == 3 && A.shift_ok) {
+#pragma unroll
+            for (int d = 0; d < D; d++) pr[d] += bwd_shift_of(ent[g], d);
         }
 #pragma unroll
         for (int k = 0; k < T; k++) Ug[g][k] = pr[D + k];
@@ -350,7 +365,8 @@ __device__ __forceinline__ void bwd_batch_centred(const BwdArgs& A, const float*
 #pragma unroll
             for (int k = 0; k < T; k++) S2[k] = S22[g][k].x + S22[g][k].y;
 #pragma unroll
-            for (int d = 0; d < D; d++) m[d] = __ldg(A.prec + (int64_t)id[g] * PW + d) - ctr[d];
+            for (int d = 0; d < D; d++)
+                m[d] = (__ldg(A.prec + (int64_t)id[g] * PW + d) + ((D == 3 && A.shift_ok) ? bwd_shift_of(ent[g], d) : 0.f)) - ctr[d];
 #pragma unroll
             for (int d = 0; d < D; d++) M1[d] = fmaf(m[d], W, -S1[d]);
             atomicAdd(A.dvalues + (int64_t)id[g] * A.C + A.ch0, W);
@@ -391,7 +407,7 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
         const int qi = lane + 32 * g;
         valid[g] = qi < count;
         const uint32_t ent = queue[valid[g] ? qi : 0];
-        id[g] = ent & ~BWD_EXACT_BIT;
+        id[g] = (D == 3 && FN == 0 && A.shift_ok) ? (ent & BWD_ID_MASK_SHIFT) : (ent & ~BWD_EXACT_BIT);
         exact[g] = (ent & BWD_EXACT_BIT) != 0u;
         const float4* p4 = (const float4*)(A.prec + (int64_t)id[g] * PW);
         float pr[PW];
@@ -401,7 +417,7 @@ __device__ __forceinline__ void bwd_batch(const BwdArgs& A, const float* __restr
             pr[q * 4] = v.x; pr[q * 4 + 1] = v.y; pr[q * 4 + 2] = v.z; pr[q * 4 + 3] = v.w;
         }
 #pragma unroll
-        for (int d = 0; d < D; d++) mu[g][d] = pr[d];
+        for (int d = 0; d < D; d++) mu[g][d] = pr[d] + ((D == 3 && FN == 0 && FAST && A.shift_ok) ? bwd_shift_of(ent, d) : 0.f);
 #pragma unroll
         for (int k = 0; k < T; k++) {
             geo[g][k] = pr[D + k];
@@ -749,9 +765,14 @@ __global__ void __launch_bounds__(BWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
 #pragma unroll
                         for (int d = 0; d < D; d++) {
                             const float xmin = m3[d] - hi[d], xmax = m3[d] - lo[d];
-                            if (!(xmin >= -1.0f && xmax <= 1.0f)) fast = false;
+                            if (!(xmin >= -1.0f && xmax <= 1.0f)) {
+                                if (D == 3 && FN == 0 && A.shift_ok && xmin > 1.0f && xmax < 2.0f) id |= 1u << (BWD_SHIFT_LSB + 2 * d);
+                                else if (D == 3 && FN == 0 && A.shift_ok && xmax < -1.0f && xmin > -2.0f) id |= 2u << (BWD_SHIFT_LSB + 2 * d);
+                                else fast = false;
+                            }
                             if (!(fabsf(xmin) < 2.0f && fabsf(xmax) < 2.0f)) exact = true;
                         }
+                        if (!fast) id &= (D == 3 && FN == 0 && A.shift_ok) ? BWD_ID_MASK_SHIFT : 0xffffffffu;   // literal path: plain id
                     }
                     const uint32_t balP = __ballot_sync(0xffffffffu, pass);
                     const uint32_t balF = __ballot_sync(0xffffffffu, pass && fast);
@@ -952,6 +973,7 @@ int dgs_launch_backward(const dgs_plan_t* plan, int fn, int C, const float* mean
     a.sched = (uint32_t*)(gbuf + plan->g_sched_off) + 1;     // the forward's counter is word 0
     a.n_tiles = (uint32_t)((int64_t)plan->n_coarse * plan->fine_per_coarse);
     a.t_max = dgs_tau_for(plan, dgs_mask_level(fn)) * 1.44269504088896340736f;
+    a.shift_ok = (plan->D == 3 && fn == 0 && plan->P < ((int64_t)1 << BWD_SHIFT_LSB)) ? 1 : 0;
     {
         // nominal fine-tile half diagonal against the smallest narrow-axis reach at this function's tau
         const float w = DGS_CELL / (float)(plan->F > 0 ? plan->F : 1);
