@@ -723,7 +723,9 @@ int dgs_launch_tile_aabb(const dgs_plan_t* plan, const float* fine_xyz, const ui
 // first L1_CAPL of them in shared memory; (B) the warp then works through ALL parked (Gaussian, tile) items 32 at a time:
 // box load + cull test + counter update (count pass), cursor grab + id store (emit pass) at full lane width.  Round 1 ran the
 // test inside the per-Gaussian loops at 10-13 active lanes per warp (ncu, profiles/r02_ncu_preprocess_blocks.txt).
-#define L1_CAPL 16
+// parked candidates per lane: 8 in the count pass, 32 in the emit pass (cfg3: count 0.80 -> 0.72 ms, emit 0.64 -> 0.57 ms against 16 / 16;
+// cfg2 indifferent; profiles/r02_sweep_list_build_parking.jsonl: v1 = 32, v2 = 24, v3 = 8 for both passes)
+#define L1_CAPL (EMIT ? 32 : 8)
 template <int D, bool EMIT>
 __global__ void __launch_bounds__(DGS_THREADS) dgs_l1_kernel(const float* __restrict__ means, const float* __restrict__ radii,
                                                              const float4* __restrict__ crec, const float* __restrict__ crecR,
@@ -931,7 +933,9 @@ int dgs_launch_l1_cursor_init(const uint32_t* start_tmp, int n, uint32_t* start_
 // were just written and sit in L2; a list can be longer than any shared-memory buffer), only the histograms are in
 // shared memory.  Replaces the two device-wide radix passes over (tile, id) pairs of round 1.
 // ------------------------------------------------------------------------------------
+#ifndef L1S_THREADS
 #define L1S_THREADS 128
+#endif
 #define L1S_WARPS (L1S_THREADS / 32)
 #define L1S_CAP 2048          // list entries sorted entirely in shared memory (2 x 8 KB); longer lists ping-pong in global memory
 
@@ -1044,7 +1048,9 @@ int dgs_launch_l1_sort(const dgs_plan_t* plan, const uint32_t* l1_start, uint32_
 // One CTA per coarse tile: the boxes of its fine tiles (centre, half width) are set up once in shared memory, the
 // threads stride over the tile's list entries.  Level thresholds that do not depend on the fine tile are formed once per
 // entry (same products as DgsCullGeom::decide, so the masks are bit-identical to testing every level from scratch).
+#ifndef DGS_MASK_THREADS
 #define DGS_MASK_THREADS 128
+#endif
 __device__ __forceinline__ float dgs_sqrt_approx(float x) {
     float y;
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
