@@ -282,7 +282,8 @@ static int choose_tiles(dgs_plan_t* pl) {
     double cells_eff = (double)(pl->blocks > 0 ? pl->blocks : 1) * ((double)pl->reserved0 * 1e-6);
     if (cells_eff < 1.0) cells_eff = 1.0;
     const double per_cell = (double)pl->N / cells_eff;
-    double target = D == 1 ? 224.0 : (D == 2 ? 170.0 : 110.0);   // samples per fine tile (profiles/r02_sweep_tile_target.jsonl: cfg2 5.43 ms at 160-176 against 5.50 at 192)
+    double target = D == 1 ? 224.0 : (D == 2 ? 192.0 : 110.0);   // samples per fine tile.  170 looked better in the warm-cache probe (profiles/r02_sweep_tile_target.jsonl)
+                                                                  // but lost under the bench's L2 flush: 5.46 ms against 5.42 at 192 (r02_bench_cfg2_g.json / _c.json)
     const int tune_target = g_tune_target.load(), tune_fpc = g_tune_fpc.load(), tune_t1 = g_tune_t1.load();
     if (tune_target >= 8) target = (double)tune_target;   // samples per fine tile
     double f = pow(per_cell / target, 1.0 / D);

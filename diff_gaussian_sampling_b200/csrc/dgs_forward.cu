@@ -337,6 +337,9 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                 float* raw = sF;
                 int nq = 0, cnt_prev = 0, cur = 0;
                 static_assert(SMAX <= 8, "at most four sample pairs per lane");
+                // D == 3: persistent sample pairs (fwd_eval_packed; cfg3 7.93 -> 7.82 ms).  D <= 2 keeps the per-record-batch
+                // form (fwd_eval_fast): the persistent pairs measured SLOWER there (cfg2 1.65 -> 1.78 ms, run r02f).
+                constexpr bool PAIRS = D == 3;
                 float2 nx2[4][D], a2[4];
 #pragma unroll
                 for (int p2 = 0; p2 < 4; p2++) {
@@ -395,15 +398,20 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         }
                         __syncwarp();
                     }
-                    fwd_flush_packed<D, PW>(sp_eff, buf, cnt, nx2, a2);
-                    if (balG) {
-                        // the literal path accumulates into the scalar accumulators: fold them into the pairs afterwards
-                        fwd_eval_general<D, FN, CB>(sG, __popc(balG), s_eff, x, acc);
+                    if constexpr (PAIRS) {
+                        fwd_flush_packed<D, PW>(sp_eff, buf, cnt, nx2, a2);
+                        if (balG) {
+                            // the literal path accumulates into the scalar accumulators: fold them into the pairs afterwards
+                            fwd_eval_general<D, FN, CB>(sG, __popc(balG), s_eff, x, acc);
 #pragma unroll
-                        for (int i = 0; i < SMAX; i++) {
-                            if (i & 1) a2[i >> 1].y += acc[i][0][0]; else a2[i >> 1].x += acc[i][0][0];
-                            acc[i][0][0] = 0.f;
+                            for (int i = 0; i < SMAX; i++) {
+                                if (i & 1) a2[i >> 1].y += acc[i][0][0]; else a2[i >> 1].x += acc[i][0][0];
+                                acc[i][0][0] = 0.f;
+                            }
                         }
+                    } else {
+                        fwd_flush_fast<D, FN, CB, PW>(s_eff, buf, cnt, x, acc);
+                        if (balG) fwd_eval_general<D, FN, CB>(sG, __popc(balG), s_eff, x, acc);
                     }
                     __syncwarp();
                 };
@@ -463,8 +471,10 @@ __global__ void __launch_bounds__(FWD_THREADS, (FN == 0 && CB == 1) ? (D <= 2 ? 
                         break;
                     }
                 }
+                if constexpr (PAIRS) {
 #pragma unroll
-                for (int i = 0; i < SMAX; i++) acc[i][0][0] = (i & 1) ? a2[i >> 1].y : a2[i >> 1].x;
+                    for (int i = 0; i < SMAX; i++) acc[i][0][0] = (i & 1) ? a2[i >> 1].y : a2[i >> 1].x;
+                }
                 goto tile_pass_done;
               }
             }
