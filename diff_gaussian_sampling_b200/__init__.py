@@ -16,6 +16,8 @@ Extensions that do not change the reference signatures:
 from __future__ import annotations
 
 import ctypes
+import functools
+import os
 from collections import OrderedDict
 
 import torch
@@ -74,12 +76,31 @@ def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
 _FN_ORDER = {"gaussian": 0, "derivative": 1, "laplacian": 2, "third": 3}
 
 
+def _nvtx(name):
+    """NVTX range `dgs/<name>` around a stage when DGS_NVTX=1 is set at import (for nsys timelines of the end-to-end
+    pipeline); otherwise the function is returned untouched."""
+    if os.environ.get("DGS_NVTX", "") not in ("1", "true", "on"):
+        return lambda f: f
+
+    def deco(f):
+        @functools.wraps(f)
+        def wrapped(*a, **k):
+            torch.cuda.nvtx.range_push("dgs/" + name)
+            try:
+                return f(*a, **k)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return wrapped
+    return deco
+
+
 class _NativeOps:
     """The twelve entry points of the reference's pybind module (ext.cpp:20-31), same names and
     positional arguments, over the C ABI."""
 
     # -- preprocess_gaussians (sample_points.cu:37-98) ----------------------------------
     @staticmethod
+    @_nvtx("preprocess/bin")
     def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, tau=None, reuse=None):
         """reuse = (sample_binning_buffer, sample_ranges) of an earlier call on the SAME samples: the sample side of
         the binning (sampleWithKeys / sort / ranges and the internal tile order) is carried over instead of rebuilt."""
@@ -135,6 +156,7 @@ class _NativeOps:
 
     # -- forward (sample_points.cu:100-143,198-297) -------------------------------------
     @staticmethod
+    @_nvtx("forward")
     def _forward(fn, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
                  sample_ranges, debug):
         lib = _lib.load()
@@ -161,6 +183,7 @@ class _NativeOps:
 
     # -- backward (sample_points.cu:145-196,299-372) ------------------------------------
     @staticmethod
+    @_nvtx("backward")
     def _backward(fn, means, values, conics, samples, num_rendered, dL_dout, binning_buffer, sample_binning_buffer,
                   ranges, sample_ranges, debug):
         lib = _lib.load()

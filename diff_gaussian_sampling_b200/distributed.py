@@ -13,6 +13,8 @@ tensors over NCCL / NVLink (bench.py --gpus N).
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -64,9 +66,16 @@ def allreduce_gradients(grad_means, grad_values, grad_conics, group=None):
     if _world(group)[1] == 1:
         return grads
     flat = _common_flat_base(grads)
-    if flat is not None:
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-        return grads
+    nvtx = os.environ.get("DGS_NVTX", "") in ("1", "true", "on") and flat is not None and flat.is_cuda
+    if nvtx:
+        torch.cuda.nvtx.range_push("dgs/allreduce")
+    try:
+        if flat is not None:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+            return grads
+    finally:
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
     flat = torch.cat([g.reshape(-1) for g in grads])
     dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     out, o = [], 0
