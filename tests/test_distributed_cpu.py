@@ -114,3 +114,24 @@ def test_two_rank_sharding_matches_single_process():
     for r in res:                                                          # every rank holds the full-gradient sum
         for x, y in ((r[5], dm), (r[6], dv), (r[7], dc)):
             assert np.max(np.abs(x - y)) <= 1e-12 * max(1.0, np.max(np.abs(y)))
+
+
+def test_bench_strong_scaling_slabs_partition_the_global_grid():
+    """bench.py --gpus N (strong scaling, BASELINE.json configs[2]): the N slabs are disjoint and together are exactly
+    the N = 1 grid, in order — so `value` counts every query point of the fixed grid once."""
+    import bench
+    bench.WORKLOADS["_tiny2"] = (2, 10, 12, 1)
+    bench.WORKLOADS["_tiny3"] = (3, 10, 6, 1)
+    try:
+        for w in ("_tiny2", "_tiny3"):
+            full = bench.make_samples(w, 0, 1, "strong")
+            for world in (2, 3, 4):
+                parts = [bench.make_samples(w, r, world, "strong") for r in range(world)]
+                assert sum(p.shape[0] for p in parts) == full.shape[0]
+                assert np.array_equal(np.concatenate(parts, 0), full)
+            # weak scaling: every rank gets a full-density lattice of the whole domain, inside the bounds
+            for r in range(3):
+                p = bench.make_samples(w, r, 3, "weak")
+                assert p.shape == full.shape and p.min() >= -1.0 and p.max() <= 1.0
+    finally:
+        del bench.WORKLOADS["_tiny2"], bench.WORKLOADS["_tiny3"]
